@@ -1,0 +1,19 @@
+# Builds the product library (CUDA, sm_100a only) and the CPU oracle (test infrastructure).
+NVCC ?= nvcc
+CSRC := constraint_solver_b200/csrc
+LIB  := constraint_solver_b200/lib/libxpbd_b200.so
+NVCCFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=false \
+             -Xcompiler -fPIC,-ffp-contract=off,-Wall -shared
+SRCS := $(wildcard $(CSRC)/*.cu)
+HDRS := $(wildcard $(CSRC)/*.cuh $(CSRC)/*.hpp) include/xpbd_b200.h
+
+all: lib oracle
+lib: $(LIB)
+$(LIB): $(SRCS) $(HDRS)
+	mkdir -p $(dir $(LIB))
+	$(NVCC) $(NVCCFLAGS) $(EXTRA) -o $@ $(SRCS)
+oracle:
+	$(MAKE) -C oracle
+clean:
+	rm -rf constraint_solver_b200/lib oracle/_build
+.PHONY: all lib oracle clean

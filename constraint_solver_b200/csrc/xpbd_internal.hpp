@@ -1,0 +1,114 @@
+// Internal host-side declarations shared by the translation units of libxpbd_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/xpbd_b200.h"
+#include "xpbd_hull.cuh"
+#include "xpbd_state.cuh"
+
+namespace xpbd {
+
+// ---- error plumbing (thread-local text behind xpbd_last_error) ---------------------------
+void set_error(const char* fmt, ...);
+int fail(int status, const char* fmt, ...);
+
+#define XPBD_CUDA_TRY(expr)                                                                         \
+    do {                                                                                            \
+        cudaError_t _e = (expr);                                                                    \
+        if (_e != cudaSuccess)                                                                      \
+            return ::xpbd::fail(XPBD_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                                __FILE__, __LINE__);                                                \
+    } while (0)
+
+// ---- host copy of a registered hull ---------------------------------------------------------
+struct HostHull {
+    std::vector<double> vertices;  // n x 3
+    std::vector<int32_t> edges;    // m x 2
+    std::vector<int32_t> face_offsets, face_indices;
+    double centroid[3];
+    double radius;  // max |v - centroid| in f64
+    xpbd_polytope view() const {
+        xpbd_polytope p;
+        p.vertices = vertices.data(); p.n_vertices = (int32_t)(vertices.size() / 3);
+        p.edges = edges.data(); p.n_edges = (int32_t)(edges.size() / 2);
+        p.face_offsets = face_offsets.data(); p.face_indices = face_indices.data();
+        p.n_faces = (int32_t)face_offsets.size() - 1;
+        p.centroid[0] = centroid[0]; p.centroid[1] = centroid[1]; p.centroid[2] = centroid[2];
+        return p;
+    }
+};
+HostHull copy_hull(const xpbd_polytope* h);
+// Packs hulls into the device blob format of xpbd_hull.cuh (planes left zero: hull_planes_kernel fills them).
+std::vector<uint32_t> pack_hull_blob(const std::vector<HostHull>& hulls);
+
+// Device hull table owned by a batch or a one-shot query.
+struct DeviceHulls {
+    uint32_t* blob = nullptr;
+    uint32_t bytes = 0;
+    int n_hulls = 0;
+    int max_verts = 0, max_faces = 0, max_edges = 0, max_face_verts = 0;
+    int upload(const std::vector<HostHull>& hulls, cudaStream_t st);  // returns xpbd_status
+    void release();
+};
+
+// ---- kernel launchers (defined in the .cu files) --------------------------------------------
+void launch_aos64_to_soa(const double* aos, const BodyArrays& s, int64_t first, int64_t n, cudaStream_t st);
+void launch_soa_to_aos64(const BodyArrays& s, double* aos, int64_t first, int64_t n, cudaStream_t st);
+void launch_broadcast_world(const BodyArrays& s, int bodies_per_world, int64_t n_bodies, cudaStream_t st);
+void launch_dyn_pack(const BodyArrays& s, float* out, int64_t first, int64_t n, cudaStream_t st);
+void launch_dyn_unpack(const float* in, const BodyArrays& s, int64_t first, int64_t n, cudaStream_t st);
+void launch_hull_planes(uint32_t* blob, int n_hulls, cudaStream_t st);
+
+struct SingleStepParams;
+struct WorldStepParams;
+
+// Device joint record (fp32): anchors in body space (or world space when body_b < 0).
+struct DeviceJoint {
+    int32_t body_a, body_b;
+    float ax, ay, az;
+    float bx, by, bz;
+    float distance;
+    float pad[3];
+};
+static_assert(sizeof(DeviceJoint) == 48, "DeviceJoint is 48 bytes");
+
+}  // namespace xpbd
+
+// The opaque handle.
+struct xpbd_batch {
+    xpbd_batch_desc desc{};
+    int64_t n_bodies = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    xpbd::BodyArrays arrays{};
+    void* state_alloc = nullptr;
+    int32_t* d_hull_ids = nullptr;  // nullptr: all hull 0
+    std::vector<xpbd::HostHull> hulls;
+    xpbd::DeviceHulls dev_hulls;
+    bool hulls_dirty = true;
+    xpbd::DeviceJoint* d_joints = nullptr;
+    // staging for AoS <-> SoA conversion (two slots for copy/convert overlap)
+    double* d_stage[2] = {nullptr, nullptr};
+    cudaEvent_t stage_free[2] = {nullptr, nullptr};
+    int64_t stage_bodies = 0;
+    float* d_dyn_stage = nullptr;  // n_bodies x 13 floats, allocated on first use
+    // stats
+    unsigned long long* d_counters = nullptr;  // [0] constraints, [1] overflow worlds, [2] tma fallbacks
+    unsigned long long* h_counters = nullptr;  // pinned
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    xpbd_step_stats last{};
+    bool stepped = false;
+    void* world_scratch = nullptr;  // owned by the multi-body path
+};
+
+namespace xpbd {
+int finalize_hulls(xpbd_batch* b);
+int step_single(xpbd_batch* b, float frame_dt, int substeps, int n_frames);
+int step_world(xpbd_batch* b, float frame_dt, int substeps, int n_frames);
+void release_world_scratch(xpbd_batch* b);
+}  // namespace xpbd

@@ -1,0 +1,124 @@
+// Fused single-body XPBD step: solver::step (src/solver.rs:3-17) for n independent bodies,
+// all substeps of all frames in ONE launch with the body state held in registers.
+//
+// Mapping: one thread per body (every body is its own world on this path: world.rs:41-42 steps
+// a and b independently, each only against the ground plane).  HBM is touched once per step
+// call: 38 floats read + 13 written per body, coalesced float4 (xpbd_state.cuh).  The hull
+// table is staged into shared memory by one TMA bulk copy per block (xpbd_tma.cuh).
+//
+// Gauss-Seidel order = hull vertex order (src/collision.rs:16).  The reference materialises a
+// Vec<Constraint> before the sweep, with contact points computed from the post-integrate pose
+// and NOT refreshed while the sweep moves the body (src/solver.rs:12-13).  Here the
+// post-integrate frame is kept in registers and each constraint is generated right before it
+// is applied — from that saved frame, so the values are identical to the reference's.
+#include "xpbd_hull.cuh"
+#include "xpbd_internal.hpp"
+#include "xpbd_rigid.cuh"
+#include "xpbd_tma.cuh"
+
+namespace xpbd {
+
+struct SingleStepParams {
+    BodyArrays bodies;
+    int64_t n_bodies;
+    const int32_t* hull_ids;  // per body, or nullptr = hull 0
+    const uint32_t* hull_blob;
+    uint32_t hull_blob_bytes;  // multiple of 16
+    float frame_dt;
+    int32_t substeps;
+    int32_t n_frames;
+    float compliance;
+    float friction;
+    unsigned long long* constraint_counter;  // += constraints applied
+    unsigned int* tma_fallback_flag;
+};
+
+// One ground constraint generated from the saved post-integrate frame and applied immediately.
+// Returns true if the vertex was below the ground (a constraint was applied).
+XD bool ground_vertex(BodyDyn& d, const BodyConst& k, const Fr& frame, const Fr& frame_inv, const Fr& past, V3 vertex,
+                      float compliance, float friction) {
+    // collision::ground (src/collision.rs:16-31)
+    V3 p = frame * vertex;
+    if (p.z >= 0.0f) return false;
+    V3 target = v3(p.x, p.y, 0.0f);
+    V3 correction = target - p;
+    V3 local = frame_inv * p;  // Frame::delta (src/frame.rs:40-44)
+    V3 delta = p - (past * local);
+    V3 delta_t = delta - project_on(delta, correction);
+    V3 c1 = target - friction * delta_t;
+    // solver::solve body (src/solver.rs:22-26), Constraint methods (src/constraint.rs:13-37)
+    V3 diff = c1 - p;
+    float dist = magnitude(diff);                  // current_distance(); distance == 0
+    V3 dir = diff * fdiv(1.0f, dist);              // direction() = normalize
+    float w = inverse_resistance(d.position, d.rotation, k.inverse_mass, k.inverse_inertia, k.center_of_mass, p, dir);
+    float lambda = fdiv(fsub(dist, 0.0f), fadd(w, compliance));
+    rigid_apply_impulse(d.position, d.rotation, k.inverse_mass, k.inverse_inertia, k.center_of_mass, lambda * dir, p);
+    return true;
+}
+
+__global__ void __launch_bounds__(128) step_single_kernel(SingleStepParams P) {
+    extern __shared__ __align__(16) uint32_t smem_blob[];
+    __shared__ __align__(8) uint64_t bar;
+    stage_bulk(smem_blob, P.hull_blob, P.hull_blob_bytes, &bar, P.tma_fallback_flag);
+
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int applied = 0;
+    if (g < P.n_bodies) {
+        HullTable hulls{smem_blob};
+        const HullDesc hd = hulls.desc(P.hull_ids ? P.hull_ids[g] : 0);
+
+        BodyDyn d;
+        BodyConst k;
+        load_dyn(P.bodies, g, d);
+        load_const(P.bodies, g, k);
+        const StepConsts sc = make_step_consts(P.frame_dt, P.substeps, P.compliance);
+        const M3 dtI = sc.dt * k.inverse_inertia;
+
+        const int total = P.n_frames * P.substeps;
+        for (int s = 0; s < total; ++s) {
+            const V3 past_position = d.position;
+            const Q4 past_rotation = d.rotation;
+            const Fr past = rigid_frame(d.position, d.rotation, k.center_of_mass);
+            rigid_integrate(d, k, dtI, sc);
+            const Fr frame = rigid_frame(d.position, d.rotation, k.center_of_mass);
+            const Fr frame_inv = frame_inverse(frame);
+            for (int v = 0; v < hd.n_verts; ++v)
+                applied += ground_vertex(d, k, frame, frame_inv, past, hulls.vertex(hd, v), sc.compliance, P.friction);
+            rigid_derive(d, past_position, past_rotation, sc.dt);
+        }
+        store_dyn(P.bodies, g, d);
+    }
+    // one atomic per warp
+    for (int o = 16; o > 0; o >>= 1) applied += __shfl_down_sync(0xffffffffu, applied, o);
+    if ((threadIdx.x & 31) == 0 && applied) atomicAdd(P.constraint_counter, (unsigned long long)applied);
+}
+
+int step_single(xpbd_batch* b, float frame_dt, int substeps, int n_frames) {
+    const uint32_t blob_bytes = b->dev_hulls.bytes;
+    if (blob_bytes > 200u * 1024u)
+        return fail(XPBD_ERR_CAPACITY, "hull table of %u bytes does not fit in shared memory", blob_bytes);
+    if (blob_bytes > 48u * 1024u)  // per-device attribute; cheap, so set on every call that needs it
+        XPBD_CUDA_TRY(cudaFuncSetAttribute(step_single_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)blob_bytes));
+    SingleStepParams P;
+    P.bodies = b->arrays;
+    P.n_bodies = b->n_bodies;
+    P.hull_ids = b->d_hull_ids;
+    P.hull_blob = b->dev_hulls.blob;
+    P.hull_blob_bytes = blob_bytes;
+    P.frame_dt = frame_dt;
+    P.substeps = substeps;
+    P.n_frames = n_frames;
+    P.compliance = (float)b->desc.compliance;
+    P.friction = (float)b->desc.friction;
+    P.constraint_counter = b->d_counters;
+    P.tma_fallback_flag = reinterpret_cast<unsigned int*>(b->d_counters + 2);
+    const int block = 128;
+    const int64_t grid = (P.n_bodies + block - 1) / block;
+    step_single_kernel<<<(unsigned)grid, block, blob_bytes, b->stream>>>(P);
+    XPBD_CUDA_TRY(cudaGetLastError());
+    b->last.kernel_launches = 1;
+    return XPBD_OK;
+}
+
+}  // namespace xpbd
