@@ -34,12 +34,10 @@ struct SingleStepParams {
 };
 
 // One ground constraint generated from the saved post-integrate frame and applied immediately.
-// Returns true if the vertex was below the ground (a constraint was applied).
-XD bool ground_vertex(BodyDyn& d, const BodyConst& k, const Fr& frame, const Fr& frame_inv, const Fr& past, V3 vertex,
-                      float compliance, float friction) {
-    // collision::ground (src/collision.rs:16-31)
-    V3 p = frame * vertex;
-    if (p.z >= 0.0f) return false;
+// `p` is the (already tested, p.z < 0) world-space vertex position.
+XD void ground_contact(BodyDyn& d, const BodyConst& k, const Fr& frame_inv, const Fr& past, V3 p, float compliance,
+                       float friction) {
+    // collision::ground (src/collision.rs:22-31)
     V3 target = v3(p.x, p.y, 0.0f);
     V3 correction = target - p;
     V3 local = frame_inv * p;  // Frame::delta (src/frame.rs:40-44)
@@ -53,7 +51,6 @@ XD bool ground_vertex(BodyDyn& d, const BodyConst& k, const Fr& frame, const Fr&
     float w = inverse_resistance(d.position, d.rotation, k.inverse_mass, k.inverse_inertia, k.center_of_mass, p, dir);
     float lambda = fdiv(fsub(dist, 0.0f), fadd(w, compliance));
     rigid_apply_impulse(d.position, d.rotation, k.inverse_mass, k.inverse_inertia, k.center_of_mass, lambda * dir, p);
-    return true;
 }
 
 __global__ void __launch_bounds__(128) step_single_kernel(SingleStepParams P) {
@@ -82,8 +79,25 @@ __global__ void __launch_bounds__(128) step_single_kernel(SingleStepParams P) {
             rigid_integrate(d, k, dtI, sc);
             const Fr frame = rigid_frame(d.position, d.rotation, k.center_of_mass);
             const Fr frame_inv = frame_inverse(frame);
-            for (int v = 0; v < hd.n_verts; ++v)
-                applied += ground_vertex(d, k, frame, frame_inv, past, hulls.vertex(hd, v), sc.compliance, P.friction);
+            // Pass 1: which vertices are below the ground (src/collision.rs:17-20), as a bit mask per lane.
+            // Pass 2: every lane walks ITS OWN set bits in ascending vertex order (= the reference's
+            // Gauss-Seidel order), so a warp iterates max-over-lanes(contacts) times instead of once per
+            // vertex slot that any lane penetrates: with mixed orientations that is ~2x fewer divergent passes.
+            for (int base = 0; base < hd.n_verts; base += 32) {
+                const int cnt = min(32, hd.n_verts - base);
+                unsigned mask = 0;
+                for (int v = 0; v < cnt; ++v) {
+                    const V3 p = frame * hulls.vertex(hd, base + v);
+                    if (!(p.z >= 0.0f)) mask |= 1u << v;
+                }
+                applied += __popc(mask);
+                while (mask) {
+                    const int v = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    const V3 p = frame * hulls.vertex(hd, base + v);
+                    ground_contact(d, k, frame_inv, past, p, sc.compliance, P.friction);
+                }
+            }
             rigid_derive(d, past_position, past_rotation, sc.dt);
         }
         store_dyn(P.bodies, g, d);
