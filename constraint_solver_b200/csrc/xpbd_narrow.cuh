@@ -1,0 +1,262 @@
+// Narrowphase between two convex hulls: the reference's SAT queries (src/collision.rs:123-197,
+// dead code there) finished into a contact manifold.
+//
+//   face_query / edge_query : warp-cooperative (lanes over faces / edge pairs, shuffle arg-max that
+//                             honours the reference's "first strict maximum wins" scan order)
+//   choose_feature          : A-face / B-face / edge-edge with Gregorius' bias towards faces
+//   face_manifold / edge_manifold : one lane per body pair (Sutherland-Hodgman clipping is sequential)
+//
+// Inputs are world-space vertices W[b][v] = Rigid::frame() * vertex, computed once per body per substep
+// and shared by the ground test and every pair the body takes part in (the reference recomputes
+// `frames.0 * vertex` inside every loop; the value is identical).
+//
+// Support functions: the reference selects the support VERTEX with max_by(total_cmp) and then takes a dot
+// product with it (src/collision.rs:138-141,182,188).  max_v dot(v, -n) == -min_v dot(n, v) exactly in
+// round-to-nearest arithmetic (negation commutes with every rounding), so only the extreme VALUE is
+// needed and vertex ties cannot change it.
+#pragma once
+#include <float.h>
+
+#include "xpbd_hull.cuh"
+
+namespace xpbd {
+
+constexpr int kMaxManifold = 4;
+constexpr int kMaxClip = 16;
+constexpr float kRelEdge = 0.90f, kRelFace = 0.98f, kAbsTol = 0.0025f;
+enum Feature : int { kNone = 0, kFaceA = 1, kFaceB = 2, kEdgeEdge = 3 };
+
+XD V3 ld3(const float* a, int i) { return v3(a[3 * i], a[3 * i + 1], a[3 * i + 2]); }
+XD void st3(float* a, int i, V3 v) { a[3 * i] = v.x; a[3 * i + 1] = v.y; a[3 * i + 2] = v.z; }
+
+// (value, index) arg-max across the warp: larger value wins, equal values -> lower index (the serial scan
+// keeps the FIRST strict maximum), index < 0 = "no candidate".  All lanes receive the result.
+XD void warp_argmax_first(float& d, int& i) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        float od = __shfl_xor_sync(0xffffffffu, d, o);
+        int oi = __shfl_xor_sync(0xffffffffu, i, o);
+        bool take = (od > d) || (od == d && oi >= 0 && (i < 0 || oi < i));
+        if (take) { d = od; i = oi; }
+    }
+}
+
+// collision::face_axes_separation (src/collision.rs:123-149) for hull A's faces against hull B's vertices.
+// L: warp-private scratch for B's vertices in A-local space (3 floats per vertex).
+XD void face_query(const HullTable& T, const HullDesc& hA, const Fr& FinvA, const float* WB, int nB, float* L, int lane,
+                   float& out_d, int& out_face) {
+    for (int v = lane; v < nB; v += 32) st3(L, v, FinvA * ld3(WB, v));  // frames.0.inverse() * (frames.1 * p)
+    __syncwarp();
+    float best = -FLT_MAX;  // f64::MIN
+    int bi = -1;            // usize::MAX
+    for (int f = lane; f < hA.n_faces; f += 32) {
+        const float4 pl = T.plane(hA, f);
+        const V3 n = v3(pl.x, pl.y, pl.z);
+        float m = dot(n, ld3(L, 0));
+        for (int v = 1; v < nB; ++v) m = fminf(m, dot(n, ld3(L, v)));
+        const float distance = fsub(m, pl.w);  // plane.distance(support)
+        if (distance > best) { best = distance; bi = f; }
+    }
+    warp_argmax_first(best, bi);
+    out_d = best;
+    out_face = bi;
+    __syncwarp();
+}
+
+// Plane::from_point_normal (src/geometry.rs:27-36): displacement only.
+XD float plane_displacement(V3 point, V3 normal) {
+    float d = magnitude(project_on(point, normal));
+    if (dot(point, normal) < 0.0f) d = fmul(d, -1.0f);
+    return d;
+}
+
+// collision::edge_axes_separation (src/collision.rs:151-197).  Edge pairs in A-major order.
+XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const float* WA, const float* WB, V3 CA,
+                   int lane, float& out_d, int& out_pair) {
+    float best = -FLT_MAX;
+    int bi = -1;
+    const int nPairs = hA.n_edges * hB.n_edges;
+    for (int e = lane; e < nPairs; e += 32) {
+        const int ia = e / hB.n_edges, jb = e - ia * hB.n_edges;
+        const int2 ea = T.edge(hA, ia), eb = T.edge(hB, jb);
+        const V3 foot = ld3(WA, ea.x);
+        const V3 edge_a = ld3(WA, ea.y) - foot;
+        const V3 edge_b = ld3(WB, eb.y) - ld3(WB, eb.x);
+        V3 axis = normalize(cross(edge_a, edge_b));  // parallel edges -> NaN axis, no guard (as the reference)
+        if (dot(axis, foot - CA) < 0.0f) axis = -axis;
+        // Ignore if another point on `a` is further in the direction to `b`.
+        float sa = dot(ld3(WA, 0), axis);
+        for (int v = 1; v < hA.n_verts; ++v) sa = fmaxf(sa, dot(ld3(WA, v), axis));
+        if (sa > dot(foot, axis)) continue;
+        const float disp = plane_displacement(foot, axis);
+        // plane.distance(B.support(-axis)) = min_v dot(axis, v) - displacement
+        float sb = dot(axis, ld3(WB, 0));
+        for (int v = 1; v < hB.n_verts; ++v) sb = fminf(sb, dot(axis, ld3(WB, v)));
+        const float distance = fsub(sb, disp);
+        if (distance > best) { best = distance; bi = e; }
+    }
+    warp_argmax_first(best, bi);
+    out_d = best;
+    out_pair = bi;
+}
+
+// Result of the three queries for one body pair, kept until the per-lane manifold pass.
+struct PairFeature {
+    int feature;  // Feature
+    int index;    // face index (kFaceA: of A, kFaceB: of B) or flat edge pair index ia * nEdgesB + jb
+};
+
+XD PairFeature choose_feature(float da, int fa, float db, int fb, float de, int epair) {
+    PairFeature r;
+    const float face_max = da > db ? da : db;
+    if (epair >= 0 && de > fadd(fmul(kRelEdge, face_max), kAbsTol)) {
+        r.feature = kEdgeEdge; r.index = epair;
+    } else if (db > fadd(fmul(kRelFace, da), kAbsTol)) {
+        r.feature = kFaceB; r.index = fb;
+    } else {
+        r.feature = kFaceA; r.index = fa;
+    }
+    return r;
+}
+
+struct Manifold {
+    int count;
+    V3 point[kMaxManifold];   // on the incident body
+    V3 target[kMaxManifold];  // on the reference body (projection on the reference plane)
+};
+
+// Clip polygon `in` (n points) against the half-space dot(s, p - o) <= 0.
+XD int clip_polygon(const V3* in, int n, V3 o, V3 s, V3* out) {
+    int m = 0;
+    for (int k = 0; k < n; ++k) {
+        const V3 p1 = in[k], p2 = in[(k + 1 == n) ? 0 : k + 1];
+        const float d1 = dot(s, p1 - o), d2 = dot(s, p2 - o);
+        const bool in1 = d1 <= 0.0f, in2 = d2 <= 0.0f;
+        if (in1 != in2) {
+            const float t = fdiv(d1, fsub(d1, d2));
+            if (m < kMaxClip) out[m++] = p1 + (p2 - p1) * t;
+        }
+        if (in2) {
+            if (m < kMaxClip) out[m++] = p2;
+        }
+    }
+    return m;
+}
+
+// Face contact: reference body R (face r, frame FR, world verts WR), incident body I.  One lane.
+XD void face_manifold(const HullTable& T, const HullDesc& hR, const HullDesc& hI, const Fr& FR, const Fr& FI,
+                      const float* WR, const float* WI, int r, Manifold& out) {
+    out.count = 0;
+    // ref_plane = frames.0 * polytopes.0.plane(face)  (src/collision.rs:66, src/frame.rs:55-64)
+    const float4 pl = T.plane(hR, r);
+    const V3 nl = v3(pl.x, pl.y, pl.z);
+    const V3 support = FR * (pl.w * nl);
+    const V3 n = FR.q * nl;
+    const float disp = plane_displacement(support, n);
+    // incident face: least dot, first strict minimum (src/collision.rs:74-85)
+    float least = FLT_MAX;
+    int inc = -1;
+    for (int k = 0; k < hI.n_faces; ++k) {
+        const float4 pk = T.plane(hI, k);
+        const float d = dot(FI.q * v3(pk.x, pk.y, pk.z), n);
+        if (d < least) { least = d; inc = k; }
+    }
+    if (inc < 0) return;
+    V3 bufA[kMaxClip], bufB[kMaxClip];
+    int cnt = 0;
+    for (int k = T.face_begin(hI, inc); k < T.face_begin(hI, inc + 1); ++k)
+        if (cnt < kMaxClip) bufA[cnt++] = ld3(WI, T.face_vertex(hI, k));
+    const int rb = T.face_begin(hR, r), nr = T.face_begin(hR, r + 1) - rb;
+    V3* src = bufA;
+    V3* dst = bufB;
+    for (int m = 0; m < nr && cnt > 0; ++m) {
+        const int m1 = (m + 1 >= nr) ? m + 1 - nr : m + 1, m2 = (m + 2 >= nr) ? m + 2 - nr : m + 2;
+        const V3 w0 = ld3(WR, T.face_vertex(hR, rb + m));
+        const V3 w1 = ld3(WR, T.face_vertex(hR, rb + m1));
+        const V3 w2 = ld3(WR, T.face_vertex(hR, rb + m2));
+        V3 s = cross(w1 - w0, n);
+        if (dot(s, w2 - w0) > 0.0f) s = -s;
+        cnt = clip_polygon(src, cnt, w0, s, dst);
+        V3* t = src; src = dst; dst = t;
+    }
+    // keep points strictly below the reference plane (compacted in place into dst)
+    float depth[kMaxClip];
+    int c = 0;
+    for (int k = 0; k < cnt; ++k) {
+        const float d = fsub(dot(n, src[k]), disp);
+        if (d < 0.0f) { dst[c] = src[k]; depth[c] = d; ++c; }
+    }
+    int keep[kMaxManifold];
+    int nk = 0;
+    if (c <= kMaxManifold) {
+        for (int k = 0; k < c; ++k) keep[nk++] = k;
+    } else {
+        int i0 = 0;
+        for (int k = 1; k < c; ++k) if (depth[k] < depth[i0]) i0 = k;
+        int i1 = -1;
+        float far = -1.0f;
+        for (int k = 0; k < c; ++k) {
+            if (k == i0) continue;
+            const float d2 = magnitude2(dst[k] - dst[i0]);
+            if (d2 > far) { far = d2; i1 = k; }
+        }
+        int i2 = -1, i3 = -1;
+        float amax = 0.0f, amin = 0.0f;
+        const V3 e01 = dst[i1] - dst[i0];
+        for (int k = 0; k < c; ++k) {
+            if (k == i0 || k == i1) continue;
+            const float area = dot(cross(e01, dst[k] - dst[i0]), n);
+            if (area > amax) { amax = area; i2 = k; }
+            if (area < amin) { amin = area; i3 = k; }
+        }
+        keep[nk++] = i0; keep[nk++] = i1;
+        if (i2 >= 0) keep[nk++] = i2;
+        if (i3 >= 0) keep[nk++] = i3;
+        for (int a = 1; a < nk; ++a)  // insertion sort: polygon order
+            for (int b = a; b > 0 && keep[b] < keep[b - 1]; --b) { int t = keep[b]; keep[b] = keep[b - 1]; keep[b - 1] = t; }
+    }
+    for (int k = 0; k < nk; ++k) {
+        const V3 p = dst[keep[k]];
+        out.point[out.count] = p;
+        out.target[out.count] = p - depth[keep[k]] * n;  // Plane::project
+        ++out.count;
+    }
+}
+
+XD float clamp01(float x) { return x < 0.0f ? 0.0f : (x > 1.0f ? 1.0f : x); }
+
+// Closest points of the two edges (Ericson 5.1.9).  One lane.
+XD void edge_manifold(V3 p1, V3 q1, V3 p2, V3 q2, Manifold& out) {
+    const V3 d1 = q1 - p1, d2 = q2 - p2, r = p1 - p2;
+    const float a = dot(d1, d1), e = dot(d2, d2), f = dot(d2, r);
+    const float c = dot(d1, r), b = dot(d1, d2);
+    const float denom = fsub(fmul(a, e), fmul(b, b));
+    float s = denom != 0.0f ? clamp01(fdiv(fsub(fmul(b, f), fmul(c, e)), denom)) : 0.0f;
+    float t = fdiv(fadd(fmul(b, s), f), e);
+    if (t < 0.0f) { t = 0.0f; s = clamp01(fdiv(-c, a)); }
+    else if (t > 1.0f) { t = 1.0f; s = clamp01(fdiv(fsub(b, c), a)); }
+    out.point[0] = p1 + d1 * s;
+    out.target[0] = p2 + d2 * t;
+    out.count = 1;
+}
+
+// Manifold of one pair from its chosen feature. `incident` = 0: contact points ride on A, 1: on B.
+XD void pair_manifold(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const Fr& FA, const Fr& FB,
+                      const float* WA, const float* WB, PairFeature pf, Manifold& m, int& incident) {
+    m.count = 0;
+    incident = 0;
+    if (pf.feature == kEdgeEdge) {
+        const int ia = pf.index / hB.n_edges, jb = pf.index - ia * hB.n_edges;
+        const int2 ea = T.edge(hA, ia), eb = T.edge(hB, jb);
+        edge_manifold(ld3(WA, ea.x), ld3(WA, ea.y), ld3(WB, eb.x), ld3(WB, eb.y), m);
+        incident = 0;
+    } else if (pf.feature == kFaceB) {
+        face_manifold(T, hB, hA, FB, FA, WB, WA, pf.index, m);  // B is the reference, A's face is clipped
+        incident = 0;
+    } else if (pf.feature == kFaceA) {
+        face_manifold(T, hA, hB, FA, FB, WA, WB, pf.index, m);
+        incident = 1;
+    }
+}
+
+}  // namespace xpbd

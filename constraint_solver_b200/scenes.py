@@ -72,10 +72,10 @@ def c3_stack(n_worlds: int, first_world: int = 0, n_cubes: int = 10, gap: float 
     out = np.empty((n_worlds, n_cubes), dtype=_abi.RIGID_DTYPE)
     out[:] = base.rec
     bitgen = np.random.Philox(key=SEED + 3)
-    assert (2 * n_cubes) % 4 == 0
-    bitgen.advance(first_world * (2 * n_cubes) // 4)
+    per_world = 4 * ((2 * n_cubes + 3) // 4)  # whole Philox counter steps per world
+    bitgen.advance(first_world * per_world // 4)
     rng = np.random.Generator(bitgen)
-    u = rng.random((n_worlds, n_cubes, 2))
+    u = rng.random((n_worlds, per_world))[:, : 2 * n_cubes].reshape(n_worlds, n_cubes, 2)
     out["position"][:, :, 0:2] = -jitter + 2.0 * jitter * u
     out["position"][:, :, 2] = gap + np.arange(n_cubes)[None, :] * (1.0 + gap)
     return out

@@ -12,13 +12,20 @@
 //   * Sutherland-Hodgman clipping of the incident face against the side planes of the reference face,
 //     points below the reference plane kept, reduced to <= 4 (README.md:18-19);
 //   * `Constraint` generalised to two bodies (src/constraint.rs:7,25,34 were shaped for it):
-//     lambda = (|c1-c0| - distance) / (w_a + w_b + compliance/dt^2), +impulse on a at c0, -impulse on b at c1;
-//   * contact friction exactly like collision::ground's (src/collision.rs:24-29): the target point is
-//     moved back by the tangential part of the RELATIVE motion of the two material points this substep;
-//   * per substep: save past, integrate all, generate ALL constraints (ground body-major, then body
-//     pairs i<j lexicographic, then joints), one Gauss-Seidel sweep in that order with stale contact
-//     points (src/solver.rs:12-13), derive all.
-// With one body, no joints and body_body = false this reduces to solver::step bit for bit.
+//     lambda = c / (w_a + w_b + compliance/dt^2), +impulse on a, -impulse on b, with the reference's
+//     inverse_resitance and apply_impulse per body.
+// Per substep: save past, integrate all bodies, generate ALL constraints from the post-integrate poses
+// (ground body-major in hull-vertex order, then body pairs i<j lexicographic, then joints), ONE
+// Gauss-Seidel sweep in that order, derive all, then one velocity pass over the contacts that were active.
+//   * Ground constraints are the reference's, unchanged: stale contact points and the position-level
+//     friction offset (src/collision.rs:13-35, src/solver.rs:12-13).  With one body, no joints and
+//     body_body = false the step reduces to solver::step bit for bit.
+//   * Body-body contacts and joints are evaluated FRESH at sweep time from body-local anchors (Mueller et
+//     al. 2020, README.md:14): measured on the 10-cube stack, stale two-body contacts cannot carry a stack
+//     (each of the n stale points re-applies the full correction; the stack explodes within 10 frames).
+//   * The velocity pass (Mueller 2020 "solveVelocities", restitution 0) removes the relative normal velocity
+//     and `friction` x the relative tangential velocity at every active contact.  Without it the
+//     penetration-recovery velocity of a compressed stack is kept by derive() and the stack bounces apart.
 #pragma once
 #include <algorithm>
 #include <array>
@@ -40,12 +47,16 @@ struct Tuning {
 
 enum ConstraintKind : int { kGround = 0, kContact = 1, kJoint = 2 };
 
+// kGround : a, b = contact0, contact1 in WORLD space (stale, as the reference), distance = 0.
+// kContact: a = point in body rigid_a's OBJECT space (the incident body), b = point on the reference plane in
+//           body rigid_b's object space, normal = world-space unit direction a must move along.
+// kJoint  : a, b = anchors in object space (b in world space when rigid_b < 0), distance = rest length.
 template <class S>
 struct Constraint2 {
     int rigid_a = 0;
     int rigid_b = -1;  // < 0: world
     int kind = kGround;
-    Vec3<S> contact0{}, contact1{};
+    Vec3<S> a{}, b{}, normal{};
     S distance{};
 };
 
@@ -232,18 +243,16 @@ Manifold<S> sat_manifold(Frame<S> fa, Frame<S> fb, const Hull<S>& ha, const Hull
     return m;
 }
 
-// Friction offset shared by every contact (generalises src/collision.rs:23-29).
-// Returns false when the correction is degenerate (|correction|^2 == 0): such a point is dropped.
+// One manifold point -> fresh contact constraint.  Dropped when point and target coincide (no direction).
 template <class S>
-bool contact_constraint(int inc, int oth, Frame<S> f_inc, Frame<S> past_inc, Frame<S> f_oth, Frame<S> past_oth,
-                        Vec3<S> point, Vec3<S> target, S friction, Constraint2<S>& out) {
+bool contact_constraint(int inc, int oth, Frame<S> f_inc, Frame<S> f_oth, Vec3<S> point, Vec3<S> target,
+                        Constraint2<S>& out) {
     Vec3<S> correction = target - point;
     if (magnitude2(correction) == S(0)) return false;
-    Vec3<S> delta = f_inc.delta(past_inc, point) - f_oth.delta(past_oth, point);
-    Vec3<S> delta_t = delta - project_on(delta, correction);
     out.rigid_a = inc; out.rigid_b = oth; out.kind = kContact;
-    out.contact0 = point;
-    out.contact1 = target - friction * delta_t;
+    out.a = f_inc.inverse() * point;
+    out.b = f_oth.inverse() * target;
+    out.normal = normalize(correction);
     out.distance = S(0);
     return true;
 }
@@ -257,7 +266,7 @@ struct WorldState {
 };
 
 template <class S>
-struct StepCounters { uint64_t constraints = 0, pairs_tested = 0, manifolds = 0; };
+struct StepCounters { uint64_t constraints = 0, pairs_tested = 0, manifolds = 0, active_contacts = 0; };
 
 template <class S>
 void generate_constraints(const WorldState<S>& w, const std::vector<Hull<S>>& hulls, const std::vector<Frame<S>>& past,
@@ -277,8 +286,8 @@ void generate_constraints(const WorldState<S>& w, const std::vector<Hull<S>>& hu
             Vec3<S> delta_t = delta - project_on(delta, correction);
             Constraint2<S> c;
             c.rigid_a = b; c.rigid_b = -1; c.kind = kGround;
-            c.contact0 = position;
-            c.contact1 = target - prm.friction * delta_t;
+            c.a = position;
+            c.b = target - prm.friction * delta_t;
             c.distance = S(0);
             out.push_back(c);
         }
@@ -298,8 +307,8 @@ void generate_constraints(const WorldState<S>& w, const std::vector<Hull<S>>& hu
                 int inc = m.incident == 0 ? i : j, oth = m.incident == 0 ? j : i;
                 for (int k = 0; k < m.count; ++k) {
                     Constraint2<S> c;
-                    if (contact_constraint(inc, oth, frames[(size_t)inc], past[(size_t)inc], frames[(size_t)oth],
-                                           past[(size_t)oth], m.point[(size_t)k], m.target[(size_t)k], prm.friction, c))
+                    if (contact_constraint(inc, oth, frames[(size_t)inc], frames[(size_t)oth], m.point[(size_t)k],
+                                           m.target[(size_t)k], c))
                         out.push_back(c);
                 }
             }
@@ -310,8 +319,7 @@ void generate_constraints(const WorldState<S>& w, const std::vector<Hull<S>>& hu
         if (j.body_a < 0) continue;
         Constraint2<S> c;
         c.rigid_a = j.body_a; c.rigid_b = j.body_b; c.kind = kJoint;
-        c.contact0 = frames[(size_t)j.body_a] * j.anchor_a;
-        c.contact1 = j.body_b >= 0 ? frames[(size_t)j.body_b] * j.anchor_b : j.anchor_b;
+        c.a = j.anchor_a; c.b = j.anchor_b;
         c.distance = j.distance;
         out.push_back(c);
     }
@@ -323,20 +331,75 @@ S inverse_resistance_at(const Rigid<S>& r, Vec3<S> contact, Vec3<S> direction) {
     return r.inverse_mass + dot(r.inverse_inertia * angular_impulse, angular_impulse);
 }
 
+// One Gauss-Seidel sweep. active[k] = 1 for every contact that was penetrating when it was solved.
 template <class S>
-void sweep(WorldState<S>& w, const std::vector<Constraint2<S>>& cs, S compliance) {
-    for (const Constraint2<S>& c : cs) {
-        Vec3<S> diff = c.contact1 - c.contact0;
-        S dist = magnitude(diff);
-        if (c.kind != kGround && dist == S(0)) continue;  // two-body/joint guard: no direction
-        Vec3<S> dir = diff * (S(1) / dist);
-        Rigid<S>& a = w.bodies[(size_t)c.rigid_a];
-        S resistance = inverse_resistance_at(a, c.contact0, dir);
-        if (c.rigid_b >= 0) resistance = resistance + inverse_resistance_at(w.bodies[(size_t)c.rigid_b], c.contact1, dir);
-        S lambda = (dist - c.distance) / (resistance + compliance);
-        Vec3<S> impulse = lambda * dir;
-        a.apply_impulse(impulse, c.contact0);
-        if (c.rigid_b >= 0) w.bodies[(size_t)c.rigid_b].apply_impulse(-impulse, c.contact1);
+void sweep(WorldState<S>& w, const std::vector<Constraint2<S>>& cs, S compliance, std::vector<char>& active) {
+    active.assign(cs.size(), 0);
+    for (size_t k = 0; k < cs.size(); ++k) {
+        const Constraint2<S>& c = cs[k];
+        Rigid<S>& A = w.bodies[(size_t)c.rigid_a];
+        if (c.kind == kGround) {
+            // solver::solve body (src/solver.rs:22-26) with the reference's Constraint methods
+            Vec3<S> diff = c.b - c.a;
+            S dist = magnitude(diff);
+            Vec3<S> dir = diff * (S(1) / dist);
+            S lambda = (dist - c.distance) / (inverse_resistance_at(A, c.a, dir) + compliance);
+            A.apply_impulse(lambda * dir, c.a);
+        } else if (c.kind == kContact) {
+            Rigid<S>& Bb = w.bodies[(size_t)c.rigid_b];
+            Vec3<S> pa = A.frame() * c.a;
+            Vec3<S> pb = Bb.frame() * c.b;
+            S depth = dot(pa - pb, c.normal);
+            if (!(depth < S(0))) continue;
+            active[k] = 1;
+            S resistance = inverse_resistance_at(A, pa, c.normal) + inverse_resistance_at(Bb, pb, c.normal);
+            S lambda = -depth / (resistance + compliance);
+            Vec3<S> impulse = lambda * c.normal;
+            A.apply_impulse(impulse, pa);
+            Bb.apply_impulse(-impulse, pb);
+        } else {
+            Vec3<S> pa = A.frame() * c.a;
+            Vec3<S> pb = c.rigid_b >= 0 ? w.bodies[(size_t)c.rigid_b].frame() * c.b : c.b;
+            Vec3<S> diff = pb - pa;
+            S dist = magnitude(diff);
+            if (dist == S(0)) continue;  // no direction
+            Vec3<S> dir = diff * (S(1) / dist);
+            S resistance = inverse_resistance_at(A, pa, dir);
+            if (c.rigid_b >= 0) resistance = resistance + inverse_resistance_at(w.bodies[(size_t)c.rigid_b], pb, dir);
+            S lambda = (dist - c.distance) / (resistance + compliance);
+            Vec3<S> impulse = lambda * dir;
+            A.apply_impulse(impulse, pa);
+            if (c.rigid_b >= 0) w.bodies[(size_t)c.rigid_b].apply_impulse(-impulse, pb);
+        }
+    }
+}
+
+// Velocity pass over the active contacts (after derive): relative velocity at the contact loses its normal
+// part and `friction` x its tangential part.  Body-space inverse inertia is applied to world-space vectors
+// directly, as Rigid::integrate does (src/rigid.rs:88).
+template <class S>
+void solve_velocities(WorldState<S>& w, const std::vector<Constraint2<S>>& cs, const std::vector<char>& active, S friction) {
+    for (size_t k = 0; k < cs.size(); ++k) {
+        if (!active[k]) continue;
+        const Constraint2<S>& c = cs[k];
+        Rigid<S>& A = w.bodies[(size_t)c.rigid_a];
+        Rigid<S>& Bb = w.bodies[(size_t)c.rigid_b];
+        Vec3<S> pa = A.frame() * c.a, pb = Bb.frame() * c.b;
+        Vec3<S> ra = pa - (A.position + A.center_of_mass), rb = pb - (Bb.position + Bb.center_of_mass);
+        Vec3<S> vrel = (A.velocity + cross(A.angular_velocity, ra)) - (Bb.velocity + cross(Bb.angular_velocity, rb));
+        S vn = dot(vrel, c.normal);
+        Vec3<S> vnormal = c.normal * vn;
+        Vec3<S> vt = vrel - vnormal;
+        Vec3<S> dv = -(vnormal + vt * friction);
+        S mag = magnitude(dv);
+        if (!(mag > S(0))) continue;
+        Vec3<S> dir = dv * (S(1) / mag);
+        S resistance = inverse_resistance_at(A, pa, dir) + inverse_resistance_at(Bb, pb, dir);
+        Vec3<S> p = dir * (mag / resistance);
+        A.velocity = A.velocity + p * A.inverse_mass;
+        A.angular_velocity = A.angular_velocity + A.inverse_inertia * cross(ra, p);
+        Bb.velocity = Bb.velocity - p * Bb.inverse_mass;
+        Bb.angular_velocity = Bb.angular_velocity - Bb.inverse_inertia * cross(rb, p);
     }
 }
 
@@ -350,6 +413,7 @@ void step_world(WorldState<S>& w, const std::vector<Hull<S>>& hulls, const World
     std::vector<Quat<S>> past_rot(B);
     std::vector<Frame<S>> past(B);
     std::vector<Constraint2<S>> cs;
+    std::vector<char> active;
     for (size_t k = 0; k < substep_count; ++k) {
         for (size_t b = 0; b < B; ++b) {
             past_pos[b] = w.bodies[b].position;
@@ -359,9 +423,13 @@ void step_world(WorldState<S>& w, const std::vector<Hull<S>>& hulls, const World
         }
         cs.clear();
         generate_constraints(w, hulls, past, prm, cs, ctr);
-        sweep(w, cs, compliance);
-        if (ctr) ctr->constraints += cs.size();
+        sweep(w, cs, compliance, active);
         for (size_t b = 0; b < B; ++b) w.bodies[b].derive(past_pos[b], past_rot[b], dt);
+        solve_velocities(w, cs, active, prm.friction);
+        if (ctr) {
+            ctr->constraints += cs.size();
+            for (char a : active) ctr->active_contacts += (uint64_t)a;
+        }
     }
 }
 

@@ -1,0 +1,60 @@
+"""ctypes access to the multi-body part of the CPU oracle (oracle/xo_world.hpp) — TEST INFRASTRUCTURE ONLY."""
+import ctypes as C
+
+import numpy as np
+
+import oracle_lib as xo
+from constraint_solver_b200 import _abi  # record layouts only (PolytopeC / JOINT_DTYPE are plain C layouts)
+
+_L = xo.lib
+_VP = C.c_void_p
+for _n in ("xo_step_worlds_f32", "xo_step_worlds_f64"):
+    getattr(_L, _n).restype = C.c_uint64
+_L.xo_step_worlds_f32.argtypes = [_VP, C.c_int64, C.c_int, _VP, C.c_int, _VP, _VP, C.c_int, C.c_double, C.c_double,
+                                  C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, _VP]
+_L.xo_step_worlds_f64.argtypes = [_VP, C.c_int64, C.c_int, _VP, C.c_int, _VP, _VP, C.c_int, C.c_double, C.c_double,
+                                  C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, _VP]
+
+
+def _hull_array(hulls):
+    """hulls: list of constraint_solver_b200.Polytope (used as plain data holders)."""
+    arr = (_abi.PolytopeC * len(hulls))()
+    for i, h in enumerate(hulls):
+        arr[i] = h.as_c()
+    return arr
+
+
+def step_worlds(rigids38, B, hulls, dt, substeps, frames, threads=1, hull_ids=None, joints=None, compliance=1e-6,
+                friction=1.0, body_body=True):
+    """step_world on n_worlds worlds of B bodies in place; `hulls` = list of Polytope or a vertex array (cube only)."""
+    from constraint_solver_b200.geometry import Polytope
+    if not isinstance(hulls, (list, tuple)):
+        hulls = [Polytope.new_cube()]
+    assert rigids38.flags["C_CONTIGUOUS"]
+    n_worlds = rigids38.size // (38 * B)
+    harr = _hull_array(hulls)
+    ids = None if hull_ids is None else np.ascontiguousarray(hull_ids, dtype=np.int32)
+    J = 0
+    jp = None
+    if joints is not None:
+        joints = np.ascontiguousarray(joints, dtype=_abi.JOINT_DTYPE).reshape(n_worlds, -1)
+        J = joints.shape[1]
+        jp = C.c_void_p(joints.ctypes.data)
+    ctr = np.zeros(3, dtype=np.uint64)
+    f32 = rigids38.dtype == np.float32
+    fn = _L.xo_step_worlds_f32 if f32 else _L.xo_step_worlds_f64
+    fn(C.c_void_p(rigids38.ctypes.data), n_worlds, B, C.cast(harr, _VP), len(hulls),
+       None if ids is None else C.c_void_p(ids.ctypes.data), jp, J, compliance, friction, 1 if body_body else 0,
+       np.float32(dt) if f32 else float(dt), substeps, frames, threads, C.c_void_p(ctr.ctypes.data))
+    return {"constraints": int(ctr[0]), "pairs_tested": int(ctr[1]), "manifolds": int(ctr[2])}
+
+
+def sat_manifold(fa7, fb7, hull_a, hull_b, dtype=np.float32):
+    fa = np.ascontiguousarray(fa7, dtype=dtype); fb = np.ascontiguousarray(fb7, dtype=dtype)
+    pts = np.zeros((4, 3), dtype=dtype); tg = np.zeros((4, 3), dtype=dtype)
+    feat = C.c_int32(0); inc = C.c_int32(0)
+    ha, hb = hull_a.as_c(), hull_b.as_c()
+    fn = _L.xo_sat_manifold_f32 if dtype == np.float32 else _L.xo_sat_manifold_f64
+    n = fn(C.c_void_p(fa.ctypes.data), C.c_void_p(fb.ctypes.data), C.byref(ha), C.byref(hb), C.c_void_p(pts.ctypes.data),
+           C.c_void_p(tg.ctypes.data), C.byref(feat), C.byref(inc))
+    return pts[:n], tg[:n], feat.value, inc.value

@@ -1,0 +1,167 @@
+"""GPU parity of the multi-body world step against the fp32 oracle
+(oracle/xo_world.hpp — the builder's own specification: the reference has no algorithm here).
+Bar: <= 1e-4 m / 1e-4 rad; asserted: bit-identical state and identical constraint counts."""
+import numpy as np
+import pytest
+
+import oracle_lib as xo
+import oracle_world as xw
+import parity
+import constraint_solver_b200 as cs
+from constraint_solver_b200 import _abi, scenes
+
+pytestmark = pytest.mark.gpu
+DT = scenes.FRAME_DT
+CUBE = cs.Polytope.new_cube()
+
+
+def _run_gpu(init, hulls, frames, substeps, hull_ids=None, joints=None, body_body=True, per_frame=False, **kw):
+    n, B = init.shape
+    J = 0 if joints is None else joints.shape[1]
+    with cs.Worlds(n, B, joints_per_world=J, body_body_contacts=body_body, **kw) as w:
+        for h in hulls:
+            w.add_hull(h)
+        if hull_ids is not None:
+            w.set_hulls(hull_ids)
+        if joints is not None:
+            w.set_joints(joints)
+        w.upload(init)
+        cons = 0
+        if per_frame:
+            for _ in range(frames):
+                w.integrate(DT, substeps, 1)
+                cons += w.stats()["constraints"]
+        else:
+            w.integrate(DT, substeps, frames)
+            cons = w.stats()["constraints"]
+        st = w.stats()
+        assert st["overflow_worlds"] == 0
+        return w.download(), cons
+
+
+def _run_cpu(init, hulls, frames, substeps, hull_ids=None, joints=None, body_body=True, **kw):
+    n, B = init.shape
+    r = xo.rigid38(init).astype(np.float32)
+    c = xw.step_worlds(r, B, list(hulls), DT, substeps, frames, threads=xo.hardware_threads(), hull_ids=hull_ids,
+                       joints=joints, body_body=body_body, **kw)
+    return r, c
+
+
+def _check(init, hulls, frames, substeps, **kw):
+    gpu, gcons = _run_gpu(init, hulls, frames, substeps, **kw)
+    cpu, c = _run_cpu(init, hulls, frames, substeps, **kw)
+    pos, rot, exact = parity.compare(gpu, cpu)
+    assert pos <= parity.POS_TOL and rot <= parity.ROT_TOL, (pos, rot)
+    assert exact, f"not bit-identical (max pos err {pos}, rot err {rot})"
+    assert gcons == c["constraints"], (gcons, c)
+    return gpu, c
+
+
+def test_single_body_world_path_equals_reference_path():
+    """B = 1 through the multi-body kernel reduces to solver::step bit for bit (ground constraints are the reference's)."""
+    init = scenes.c2_perturbed(512)
+    gpu, _ = _run_gpu(init, [CUBE], 60, 25, body_body=True)
+    r = xo.rigid38(init).astype(np.float32)
+    xo.step_bodies(r, CUBE.vertices, DT, 25, 60, threads=4)
+    assert np.array_equal(xo.rigid38(gpu), r.astype(np.float64))
+
+
+@pytest.mark.parametrize("frames", [1, 10, 60])
+def test_c3_stack_parity(frames):
+    init = scenes.c3_stack(64)
+    gpu, c = _check(init, [CUBE], frames, 20)
+    if frames >= 10:
+        assert c["manifolds"] > 0
+
+
+def test_c3_stack_long_run_stays_a_stack():
+    """600 frames: parity on every world + physical sanity."""
+    init = scenes.c3_stack(32)
+    gpu, _ = _check(init, [CUBE], 600, 20)
+    g = xo.rigid38(gpu).reshape(32, 10, 38)
+    assert np.isfinite(g).all()
+    dz = g[:, :, 33] - np.arange(10)[None, :]
+    assert np.abs(dz).max() < 0.02, "cubes left their level in the stack"
+    assert np.abs(g[:, :, 31:33]).max() < 0.6, "stack slid apart"
+    assert np.abs(g[:, :, 22:28]).max() < 1.0, "stack did not come to rest"
+
+
+def test_per_frame_launches_equal_fused_launch():
+    init = scenes.c3_stack(16)
+    a, ca = _run_gpu(init, [CUBE], 12, 20)
+    b, cb = _run_gpu(init, [CUBE], 12, 20, per_frame=True)
+    assert np.array_equal(xo.rigid38(a), xo.rigid38(b)) and ca == cb
+
+
+def test_tumbling_pile_of_mixed_hulls():
+    """Random poses: exercises separated pairs, all three contact features and face/edge ties."""
+    hulls = [CUBE, cs.Polytope.new_icosahedron().scaled(0.6), cs.Polytope.new_tetrahedron()]
+    n, B = 96, 6
+    rng = np.random.default_rng(5)
+    init = np.empty((n, B), dtype=_abi.RIGID_DTYPE)
+    ids = rng.integers(0, 3, (n, B)).astype(np.int32)
+    for k, h in enumerate(hulls):
+        r = cs.Rigid(h.rigid_metrics(0.5))
+        r.external_force = (0.0, 0.0, -2.0 / r.inverse_mass * 0.1)
+        init[ids == k] = r.rec
+    init["position"][:, :, 0:2] = rng.uniform(-0.6, 0.6, (n, B, 2))
+    init["position"][:, :, 2] = 0.3 + 1.1 * np.arange(B)[None, :] + rng.uniform(0, 0.2, (n, B))
+    init["rotation"] = scenes.random_unit_quaternions(rng, n * B).reshape(n, B, 4)
+    init["angular_velocity"] = rng.uniform(-2, 2, (n, B, 3))
+    _, c = _check(init, hulls, 90, 20, hull_ids=ids)
+    assert c["manifolds"] > 1000
+
+
+def test_joints_chain_without_body_contacts():
+    """Distance joints (Constraint.distance, src/constraint.rs:9): a hanging chain of cubes, one end pinned to the world."""
+    n, B = 48, 5
+    rng = np.random.default_rng(8)
+    init = np.empty((n, B), dtype=_abi.RIGID_DTYPE)
+    base = scenes.cube_rigid(0.1); base.external_force = (0, 0, -2.0)
+    init[:] = base.rec
+    init["position"][:, :, 0] = 1.5 * np.arange(B)[None, :]
+    init["position"][:, :, 2] = 6.0
+    init["velocity"] = rng.uniform(-0.5, 0.5, (n, B, 3))
+    joints = np.zeros((n, B), dtype=_abi.JOINT_DTYPE)
+    joints["body_a"][:, 0] = 0; joints["body_b"][:, 0] = -1
+    joints["anchor_a"][:, 0] = (0.5, 0.5, 1.0); joints["anchor_b"][:, 0] = (0.5, 0.5, 7.5); joints["distance"][:, 0] = 0.5
+    for k in range(1, B):
+        joints["body_a"][:, k] = k - 1; joints["body_b"][:, k] = k
+        joints["anchor_a"][:, k] = (1.0, 0.5, 0.5); joints["anchor_b"][:, k] = (0.0, 0.5, 0.5); joints["distance"][:, k] = 0.5
+    joints["body_a"][::7, B - 1] = -1  # inactive slots are skipped
+    gpu, c = _check(init, [CUBE], 120, 20, joints=joints, body_body=False)
+    g = xo.rigid38(gpu).reshape(n, B, 38)
+    assert np.isfinite(g).all() and c["constraints"] > 0
+
+
+def test_stack_with_attachment_joints_and_contacts():
+    n, B = 32, 4
+    init = scenes.c3_stack(n, n_cubes=B)
+    joints = np.zeros((n, 2), dtype=_abi.JOINT_DTYPE)
+    joints["body_a"][:, 0] = 0; joints["body_b"][:, 0] = 1
+    joints["anchor_a"][:, 0] = (0.5, 0.5, 1.0); joints["anchor_b"][:, 0] = (0.5, 0.5, 0.0); joints["distance"][:, 0] = 0.0
+    joints["body_a"][:, 1] = 2; joints["body_b"][:, 1] = 3
+    joints["anchor_a"][:, 1] = (0.0, 0.0, 1.0); joints["anchor_b"][:, 1] = (0.0, 0.0, 0.0); joints["distance"][:, 1] = 0.1
+    _check(init, [CUBE], 60, 20, joints=joints)
+
+
+def test_ragged_world_count_and_friction_compliance_params():
+    init = scenes.c3_stack(13, n_cubes=3)  # not a multiple of the worlds-per-block
+    _check(init, [CUBE], 30, 10, friction=0.5, compliance=1e-5)
+
+
+def test_c3_full_size_properties_and_sampled_parity():
+    """C3 at BASELINE size (100k worlds x 10 cubes): duplicated worlds give identical results, no NaN, no
+    overflow, stacks stay stacks; a sample of worlds is compared with the oracle."""
+    n = 100_000
+    init = scenes.c3_stack(n)
+    init[1::2] = init[0::2]
+    frames = 20
+    gpu, _ = _run_gpu(init, [CUBE], frames, 20)
+    g = xo.rigid38(gpu).reshape(n, 10, 38)
+    assert np.isfinite(g).all()
+    assert np.array_equal(g[0::2], g[1::2])
+    assert np.abs(g[:, :, 33] - np.arange(10)[None, :]).max() < 0.02
+    idx = np.arange(0, n, 1563)
+    cpu, _ = _run_cpu(init[idx], [CUBE], frames, 20)
+    assert np.array_equal(g[idx].reshape(-1, 38), cpu.astype(np.float64))
