@@ -173,6 +173,8 @@ int xpbd_batch_set_joints(xpbd_batch* b, int64_t first_world, int64_t n_worlds, 
         const xpbd_joint& j = joints[i];
         if (j.body_a >= b->desc.bodies_per_world || j.body_b >= b->desc.bodies_per_world)
             return fail(XPBD_ERR_INVALID, "joint %lld: body index out of range", (long long)i);
+        if (j.body_a >= 0 && j.body_a == j.body_b)
+            return fail(XPBD_ERR_INVALID, "joint %lld: body_a == body_b", (long long)i);
         DeviceJoint& d = host[(size_t)i];
         std::memset(&d, 0, sizeof d);
         d.body_a = j.body_a; d.body_b = j.body_b;   // body_a < 0: inactive slot

@@ -26,8 +26,14 @@ constexpr int kMaxClip = 16;
 constexpr float kRelEdge = 0.90f, kRelFace = 0.98f, kAbsTol = 0.0025f;
 enum Feature : int { kNone = 0, kFaceA = 1, kFaceB = 2, kEdgeEdge = 3 };
 
-XD V3 ld3(const float* a, int i) { return v3(a[3 * i], a[3 * i + 1], a[3 * i + 2]); }
-XD void st3(float* a, int i, V3 v) { a[3 * i] = v.x; a[3 * i + 1] = v.y; a[3 * i + 2] = v.z; }
+// World-space / local vertex arrays are float4 per vertex (x, y, z, 0), 16-byte aligned: one LDS.128 per vertex.
+XD V3 ld3(const float* a, int i) {
+    const float4 v = reinterpret_cast<const float4*>(a)[i];
+    return v3(v.x, v.y, v.z);
+}
+XD void st3(float* a, int i, V3 v) { reinterpret_cast<float4*>(a)[i] = make_float4(v.x, v.y, v.z, 0.0f); }
+constexpr int kVertWords = 4;      // words per vertex in those arrays
+constexpr int kEdgeQueueWords = 4 * 64;  // warp-private survivor queue of edge_query (axis.xyz, pair index)
 
 // (value, index) arg-max across the warp: larger value wins, equal values -> lower index (the serial scan
 // keeps the FIRST strict maximum), index < 0 = "no candidate".  All lanes receive the result.
@@ -71,30 +77,65 @@ XD float plane_displacement(V3 point, V3 normal) {
 }
 
 // collision::edge_axes_separation (src/collision.rs:151-197).  Edge pairs in A-major order.
+// Two passes over the Cartesian product so that the expensive second half only runs on the pairs that survive
+// the reference's "no vertex of A further along the axis than the edge foot" test (~40 % for cubes):
+//   pass 1 (lanes over edge pairs): axis, orientation flip, support scan of A; survivors are pushed, in order,
+//          into the warp-private queue Q (ballot compaction);
+//   pass 2 (whenever 32 survivors are queued, and once at the end): plane displacement, support scan of B,
+//          distance; lane-local arg-max with the explicit "lower pair index wins ties" rule, which is what the
+//          serial scan's strict `>` amounts to (src/collision.rs:190).
+// Every value is computed by the same expression as before; only the schedule differs.
 XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const float* WA, const float* WB, V3 CA,
-                   int lane, float& out_d, int& out_pair) {
+                   float* Q, int lane, float& out_d, int& out_pair) {
     float best = -FLT_MAX;
     int bi = -1;
-    const int nPairs = hA.n_edges * hB.n_edges;
-    for (int e = lane; e < nPairs; e += 32) {
-        const int ia = e / hB.n_edges, jb = e - ia * hB.n_edges;
-        const int2 ea = T.edge(hA, ia), eb = T.edge(hB, jb);
-        const V3 foot = ld3(WA, ea.x);
-        const V3 edge_a = ld3(WA, ea.y) - foot;
-        const V3 edge_b = ld3(WB, eb.y) - ld3(WB, eb.x);
-        V3 axis = normalize(cross(edge_a, edge_b));  // parallel edges -> NaN axis, no guard (as the reference)
-        if (dot(axis, foot - CA) < 0.0f) axis = -axis;
-        // Ignore if another point on `a` is further in the direction to `b`.
-        float sa = dot(ld3(WA, 0), axis);
-        for (int v = 1; v < hA.n_verts; ++v) sa = fmaxf(sa, dot(ld3(WA, v), axis));
-        if (sa > dot(foot, axis)) continue;
+    const int nEb = hB.n_edges, nPairs = hA.n_edges * nEb;
+    const int nA = hA.n_verts, nB = hB.n_verts;
+    float4* Q4v = reinterpret_cast<float4*>(Q);
+    auto second_half = [&](float4 q) {
+        const V3 axis = v3(q.x, q.y, q.z);
+        const int e = __float_as_int(q.w);
+        const int ia = e / nEb;
+        const V3 foot = ld3(WA, T.edge(hA, ia).x);
         const float disp = plane_displacement(foot, axis);
         // plane.distance(B.support(-axis)) = min_v dot(axis, v) - displacement
         float sb = dot(axis, ld3(WB, 0));
-        for (int v = 1; v < hB.n_verts; ++v) sb = fminf(sb, dot(axis, ld3(WB, v)));
+        for (int v = 1; v < nB; ++v) sb = fminf(sb, dot(axis, ld3(WB, v)));
         const float distance = fsub(sb, disp);
-        if (distance > best) { best = distance; bi = e; }
+        if (distance > best || (distance == best && e < bi)) { best = distance; bi = e; }
+    };
+    int qn = 0;  // warp-uniform
+    int ia = 0, jb = lane;
+    for (int e0 = 0; e0 < nPairs; e0 += 32) {
+        const int e = e0 + lane;
+        while (jb >= nEb) { jb -= nEb; ++ia; }
+        bool pass = false;
+        V3 axis = v3(0.f, 0.f, 0.f);
+        if (e < nPairs) {
+            const int2 ea = T.edge(hA, ia), eb = T.edge(hB, jb);
+            const V3 foot = ld3(WA, ea.x);
+            const V3 edge_a = ld3(WA, ea.y) - foot;
+            const V3 edge_b = ld3(WB, eb.y) - ld3(WB, eb.x);
+            axis = normalize(cross(edge_a, edge_b));  // parallel edges -> NaN axis, no guard (as the reference)
+            if (dot(axis, foot - CA) < 0.0f) axis = -axis;
+            // Ignore if another point on `a` is further in the direction to `b`.
+            float sa = dot(ld3(WA, 0), axis);
+            for (int v = 1; v < nA; ++v) sa = fmaxf(sa, dot(ld3(WA, v), axis));
+            pass = !(sa > dot(foot, axis));
+        }
+        jb += 32;
+        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        if (pass) Q4v[qn + __popc(m & ((1u << lane) - 1u))] = make_float4(axis.x, axis.y, axis.z, __int_as_float(e));
+        qn += __popc(m);
+        __syncwarp();
+        if (qn >= 32) {
+            qn -= 32;
+            second_half(Q4v[qn + lane]);
+            __syncwarp();
+        }
     }
+    if (lane < qn) second_half(Q4v[lane]);
+    __syncwarp();
     warp_argmax_first(best, bi);
     out_d = best;
     out_pair = bi;

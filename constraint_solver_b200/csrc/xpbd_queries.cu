@@ -136,10 +136,11 @@ __global__ void solve_kernel(double* rigids, int64_t n, const double* cons, cons
 // ---- pair queries: one warp per frame pair, hull 0 = A, hull 1 = B in the blob ----------------------
 constexpr int kQueryMaxVerts = 256;
 
-struct PairScratch {
-    float WA[3 * kQueryMaxVerts];
-    float WB[3 * kQueryMaxVerts];
-    float L[3 * kQueryMaxVerts];
+struct __align__(16) PairScratch {
+    float WA[kVertWords * kQueryMaxVerts];
+    float WB[kVertWords * kQueryMaxVerts];
+    float L[kVertWords * kQueryMaxVerts];
+    float Q[kEdgeQueueWords];
 };
 
 XD void pair_setup(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const Fr& FA, const Fr& FB, PairScratch& s,
@@ -170,7 +171,7 @@ __global__ void __launch_bounds__(32) pair_query_kernel(const double* fa, const 
     const V3 CA = FA * T.centroid(hA);
     if (mode == 1) {
         float d; int e;
-        edge_query(T, hA, hB, s.WA, s.WB, CA, lane, d, e);
+        edge_query(T, hA, hB, s.WA, s.WB, CA, s.Q, lane, d, e);
         if (lane == 0) {
             out_d[i] = d;
             out_i[2 * i] = e < 0 ? -1 : e / hB.n_edges;
@@ -184,7 +185,7 @@ __global__ void __launch_bounds__(32) pair_query_kernel(const double* fa, const 
     face_query(T, hA, frame_inverse(FA), s.WB, hB.n_verts, s.L, lane, da, fA);
     bool hit = !(da >= 0.0f);
     if (hit) { face_query(T, hB, frame_inverse(FB), s.WA, hA.n_verts, s.L, lane, db, fB); hit = !(db >= 0.0f); }
-    if (hit) { edge_query(T, hA, hB, s.WA, s.WB, CA, lane, de, ep); hit = !(de >= 0.0f); }
+    if (hit) { edge_query(T, hA, hB, s.WA, s.WB, CA, s.Q, lane, de, ep); hit = !(de >= 0.0f); }
     if (lane == 0) {
         Manifold m; m.count = 0;
         int incident = 0;
