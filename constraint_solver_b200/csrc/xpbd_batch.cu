@@ -1,6 +1,7 @@
 // C ABI, batch part: lifetime, hulls/joints, state upload/download, the step call.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -38,6 +39,18 @@ int ensure_stage(xpbd_batch* b) {
 }
 
 }  // namespace
+
+namespace xpbd {
+// Multi-body path selection.  XPBD_WORLD_PATH=fused|staged overrides; default: the staged pipeline for batches
+// large enough to fill the GPU per stage, the fused single-launch kernel for small ones (latency-bound).
+int step_world(xpbd_batch* b, float frame_dt, int substeps, int n_frames) {
+    const char* v = getenv("XPBD_WORLD_PATH");
+    bool staged = b->desc.n_worlds >= 4096;
+    if (v && !strcmp(v, "fused")) staged = false;
+    if (v && !strcmp(v, "staged")) staged = true;
+    return staged ? step_world_staged(b, frame_dt, substeps, n_frames) : step_world_fused(b, frame_dt, substeps, n_frames);
+}
+}  // namespace xpbd
 
 extern "C" {
 

@@ -109,6 +109,8 @@ struct xpbd_batch {
 namespace xpbd {
 int finalize_hulls(xpbd_batch* b);
 int step_single(xpbd_batch* b, float frame_dt, int substeps, int n_frames);
-int step_world(xpbd_batch* b, float frame_dt, int substeps, int n_frames);
+int step_world_fused(xpbd_batch* b, float frame_dt, int substeps, int n_frames);   // xpbd_world.cu
+int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames);  // xpbd_staged.cu
+int step_world(xpbd_batch* b, float frame_dt, int substeps, int n_frames);         // picks one of the two
 void release_world_scratch(xpbd_batch* b);
 }  // namespace xpbd

@@ -21,6 +21,7 @@
 #include "xpbd_internal.hpp"
 #include "xpbd_narrow.cuh"
 #include "xpbd_rigid.cuh"
+#include "xpbd_solve.cuh"
 #include "xpbd_tma.cuh"
 #include "xpbd_world.cuh"
 
@@ -266,26 +267,25 @@ XD int phase_joints(float* R, const WorldLayout& L, const DeviceJoint* joints, i
     return n_cons;
 }
 
-// ---- phase 2: a lane pair per world — Gauss-Seidel sweep, derive, velocity pass -------------------------
-XD float body_inverse_resistance(const float* R, const WorldLayout& L, int b, V3 contact, V3 direction) {
-    return inverse_resistance(sld3(R + L.pos, L.B, b), sldq(R + L.rot, L.B, b), R[L.invm + b], sldm(R + L.inertia, L.B, b),
-                              sld3(R + L.com, L.B, b), contact, direction);
-}
-XD void body_apply_impulse(float* R, const WorldLayout& L, int b, V3 impulse, V3 point) {
-    V3 position = sld3(R + L.pos, L.B, b);
-    Q4 rotation = sldq(R + L.rot, L.B, b);
-    rigid_apply_impulse(position, rotation, R[L.invm + b], sldm(R + L.inertia, L.B, b), sld3(R + L.com, L.B, b), impulse, point);
-    sst3(R + L.pos, L.B, b, position);
-    sstq(R + L.rot, L.B, b, rotation);
-}
-// exchange with the other lane of the pair (pm = the pair's two-lane mask)
-XD float swap1(float v, unsigned pm) { return __shfl_xor_sync(pm, v, 1); }
-XD V3 swap3(V3 v, unsigned pm) { return v3(swap1(v.x, pm), swap1(v.y, pm), swap1(v.z, pm)); }
+// ---- phase 2: a lane pair per world — Gauss-Seidel sweep, derive, velocity pass (xpbd_solve.cuh) -----------
+struct SmemBodies {  // body accessor over a world's persistent shared-memory region
+    float* R;
+    const WorldLayout& L;
+    XD V3 pos(int b) const { return sld3(R + L.pos, L.B, b); }
+    XD Q4 rot(int b) const { return sldq(R + L.rot, L.B, b); }
+    XD V3 com(int b) const { return sld3(R + L.com, L.B, b); }
+    XD float invm(int b) const { return R[L.invm + b]; }
+    XD M3 inertia(int b) const { return sldm(R + L.inertia, L.B, b); }
+    XD V3 vel(int b) const { return sld3(R + L.vel, L.B, b); }
+    XD V3 ang(int b) const { return sld3(R + L.ang, L.B, b); }
+    XD V3 ppos(int b) const { return sld3(R + L.ppos, L.B, b); }
+    XD Q4 prot(int b) const { return sldq(R + L.prot, L.B, b); }
+    XD void set_pose(int b, V3 p, Q4 q) { sst3(R + L.pos, L.B, b, p); sstq(R + L.rot, L.B, b, q); }
+    XD void set_vel(int b, V3 v, V3 w) { sst3(R + L.vel, L.B, b, v); sst3(R + L.ang, L.B, b, w); }
+};
 
-// side 0 owns the constraint's body a, side 1 its body b.  Values that the serial specification computes once
-// (depth, lambda, direction) are computed redundantly by both lanes from identical inputs.
 XD void solve_world(float* R, const WorldLayout& L, int n_cons, const StepConsts& sc, float friction, int side, unsigned pm) {
-    const int B = L.B;
+    SmemBodies A{R, L};
     // --- sweep, in list order
     for (int k = 0; k < n_cons; ++k) {
         __syncwarp(pm);  // the other lane's writes of the previous constraint are visible
@@ -293,81 +293,26 @@ XD void solve_world(float* R, const WorldLayout& L, int n_cons, const StepConsts
         const int head = reinterpret_cast<const int*>(c)[0];
         const int kind = head_kind(head), a = head_a(head), b = head_b(head);
         if (kind == kGround) {
-            if (side == 0) {
-                const V3 c0 = v3(c[1], c[2], c[3]), dir = v3(c[4], c[5], c[6]);
-                const float dist = c[7];
-                const float w = body_inverse_resistance(R, L, a, c0, dir);
-                const float lambda = fdiv(fsub(dist, 0.0f), fadd(w, sc.compliance));
-                body_apply_impulse(R, L, a, lambda * dir, c0);
-            }
+            if (side == 0) solve_ground(A, a, v3(c[1], c[2], c[3]), v3(c[4], c[5], c[6]), c[7], sc);
         } else if (kind == kContact) {
-            const V3 n = v3(c[7], c[8], c[9]);
-            const int me = side ? b : a;
-            const V3 p_me = body_frame(R, L, me) * (side ? v3(c[4], c[5], c[6]) : v3(c[1], c[2], c[3]));
-            const V3 p_ot = swap3(p_me, pm);
-            const float depth = side ? dot(p_ot - p_me, n) : dot(p_me - p_ot, n);  // dot(pa - pb, n)
-            if (!(depth < 0.0f)) continue;
-            if (side == 0) reinterpret_cast<int*>(c)[0] = head | kActiveBit;
-            const float w_me = body_inverse_resistance(R, L, me, p_me, n);
-            const float resistance = fadd(w_me, swap1(w_me, pm));  // w_a + w_b (IEEE addition commutes)
-            const float lambda = fdiv(-depth, fadd(resistance, sc.compliance));
-            const V3 impulse = lambda * n;
-            body_apply_impulse(R, L, me, side ? -impulse : impulse, p_me);
+            const bool active = solve_contact(A, side, pm, side ? b : a, side ? v3(c[4], c[5], c[6]) : v3(c[1], c[2], c[3]),
+                                              v3(c[7], c[8], c[9]), sc);
+            if (active && side == 0) reinterpret_cast<int*>(c)[0] = head | kActiveBit;
         } else {
-            const V3 anchor = side ? v3(c[4], c[5], c[6]) : v3(c[1], c[2], c[3]);
-            const int me = side ? b : a;
-            const V3 p_me = me >= 0 ? body_frame(R, L, me) * anchor : anchor;  // b < 0: world-space anchor
-            const V3 p_ot = swap3(p_me, pm);
-            const V3 diff = side ? p_me - p_ot : p_ot - p_me;  // pb - pa
-            const float dist = magnitude(diff);
-            if (dist == 0.0f) continue;
-            const V3 dir = diff * fdiv(1.0f, dist);
-            const float w_me = me >= 0 ? body_inverse_resistance(R, L, me, p_me, dir) : 0.0f;
-            const float w_ot = swap1(w_me, pm);
-            const float w_a = side ? w_ot : w_me, w_b = side ? w_me : w_ot;
-            const float resistance = b >= 0 ? fadd(w_a, w_b) : w_a;
-            const float lambda = fdiv(fsub(dist, c[7]), fadd(resistance, sc.compliance));
-            const V3 impulse = lambda * dir;
-            if (me >= 0) body_apply_impulse(R, L, me, side ? -impulse : impulse, p_me);
+            solve_joint(A, side, pm, side ? b : a, b >= 0, side ? v3(c[4], c[5], c[6]) : v3(c[1], c[2], c[3]), c[7], sc);
         }
     }
     __syncwarp(pm);
-    // --- Rigid::derive for every body (src/rigid.rs:101-109), bodies split between the two lanes
-    for (int b = side; b < B; b += 2) {
-        BodyDyn d;
-        d.position = sld3(R + L.pos, B, b); d.rotation = sldq(R + L.rot, B, b);
-        rigid_derive(d, sld3(R + L.ppos, B, b), sldq(R + L.prot, B, b), sc.dt);
-        sst3(R + L.vel, B, b, d.velocity); sst3(R + L.ang, B, b, d.angular_velocity);
-    }
+    // --- Rigid::derive for every body, bodies split between the two lanes
+    for (int b = side; b < L.B; b += 2) derive_body(A, b, sc.dt);
     // --- velocity pass over the contacts that were active in the sweep
     for (int k = 0; k < n_cons; ++k) {
         __syncwarp(pm);
         const float* c = R + L.cons + kConsWords * k;
         const int head = reinterpret_cast<const int*>(c)[0];
         if ((head & (3 | kActiveBit)) != (kContact | kActiveBit)) continue;
-        const int me = side ? head_b(head) : head_a(head);
-        const V3 n = v3(c[7], c[8], c[9]);
-        const V3 p_me = body_frame(R, L, me) * (side ? v3(c[4], c[5], c[6]) : v3(c[1], c[2], c[3]));
-        const V3 r_me = p_me - (sld3(R + L.pos, B, me) + sld3(R + L.com, B, me));
-        V3 v_me = sld3(R + L.vel, B, me), w_me = sld3(R + L.ang, B, me);
-        const V3 u_me = v_me + cross(w_me, r_me);
-        const V3 u_ot = swap3(u_me, pm);
-        const V3 vrel = side ? u_ot - u_me : u_me - u_ot;  // (va + wa x ra) - (vb + wb x rb)
-        const float vn = dot(vrel, n);
-        const V3 vnormal = n * vn;
-        const V3 vt = vrel - vnormal;
-        const V3 dv = -(vnormal + vt * friction);
-        const float mag = magnitude(dv);
-        if (!(mag > 0.0f)) continue;
-        const V3 dir = dv * fdiv(1.0f, mag);
-        const float res_me = body_inverse_resistance(R, L, me, p_me, dir);
-        const float resistance = fadd(res_me, swap1(res_me, pm));
-        const V3 p = dir * fdiv(mag, resistance);
-        const V3 dlin = p * R[L.invm + me];
-        const V3 dang = sldm(R + L.inertia, B, me) * cross(r_me, p);
-        if (side) { v_me = v_me - dlin; w_me = w_me - dang; }
-        else      { v_me = v_me + dlin; w_me = w_me + dang; }
-        sst3(R + L.vel, B, me, v_me); sst3(R + L.ang, B, me, w_me);
+        velocity_contact(A, side, pm, side ? head_b(head) : head_a(head),
+                         side ? v3(c[4], c[5], c[6]) : v3(c[1], c[2], c[3]), v3(c[7], c[8], c[9]), friction);
     }
     __syncwarp(pm);
 }
@@ -483,7 +428,6 @@ __global__ void __launch_bounds__(kWorldThreads) step_world_kernel(WorldStepPara
     if (applied) atomicAdd(P.counters, applied);
 }
 
-void release_world_scratch(xpbd_batch* b) { b->world_scratch = nullptr; }
 
 // Tuning knobs (environment, read once): XPBD_WORLD_NW = resident worlds per block, XPBD_WORLD_WARPS = warps per block.
 static int env_int(const char* name, int fallback) {
@@ -491,7 +435,7 @@ static int env_int(const char* name, int fallback) {
     return v && *v ? atoi(v) : fallback;
 }
 
-int step_world(xpbd_batch* b, float frame_dt, int substeps, int n_frames) {
+int step_world_fused(xpbd_batch* b, float frame_dt, int substeps, int n_frames) {
     const int B = b->desc.bodies_per_world, J = b->desc.joints_per_world;
     const DeviceHulls& H = b->dev_hulls;
     if (B > 1024) return fail(XPBD_ERR_CAPACITY, "bodies_per_world > 1024");

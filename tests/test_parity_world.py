@@ -12,6 +12,15 @@ from constraint_solver_b200 import _abi, scenes
 
 pytestmark = pytest.mark.gpu
 DT = scenes.FRAME_DT
+
+
+@pytest.fixture(autouse=True, params=["staged", "fused"])
+def world_path(request, monkeypatch):
+    """Every test runs on both multi-body paths: the staged pipeline (xpbd_staged.cu) and the fused
+    single-launch kernel (xpbd_world.cu).  The library reads XPBD_WORLD_PATH at each step call."""
+    monkeypatch.setenv("XPBD_WORLD_PATH", request.param)
+    return request.param
+
 CUBE = cs.Polytope.new_cube()
 
 
