@@ -4,7 +4,7 @@ CSRC := constraint_solver_b200/csrc
 LIB  := constraint_solver_b200/lib/libxpbd_b200.so
 NVCCFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=false \
              -Xcompiler -fPIC,-ffp-contract=off,-Wall -shared
-SRCS := $(wildcard $(CSRC)/*.cu)
+SRCS := $(wildcard $(CSRC)/*.cu) $(wildcard $(CSRC)/*.cpp)
 HDRS := $(wildcard $(CSRC)/*.cuh $(CSRC)/*.hpp) include/xpbd_b200.h
 
 all: lib oracle

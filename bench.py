@@ -34,7 +34,12 @@ WORKLOADS = {
                desc="C2: 2^20 perturbed single-cube-on-ground worlds per GPU (BASELINE.json configs[1])"),
     "c3": dict(worlds=100_000, bodies=10, substeps=20, preroll=30,
                desc="C3/C5: 10-cube stack per world, 100k worlds per GPU, 20 substeps/frame (configs[2], [4])"),
+    "c4": dict(worlds=16_384, bodies=64, substeps=20, preroll=20,
+               desc="C4: 64-body pile of mixed QuickHull hulls with 32 distance joints per world, 16k worlds (configs[3])"),
 }
+# Default = C3: the configuration BASELINE.json's target (>= 1e9 body-substeps/s per B200) and its weak-scaling
+# sweep (configs[4]: the same worlds sharded over 1/2/4/8 GPUs) are quoted on.  `--workload c2` is configs[1].
+DEFAULT_WORKLOAD = "c3"
 BYTES_PER_BODY_PER_STEP = 204  # 38 floats read + 13 written
 
 
@@ -107,12 +112,16 @@ class ClockSampler(threading.Thread):
 
 
 def make_scene(workload: str, n_worlds: int, first_world: int):
+    """Returns (rigids, hulls, body_body, extras) with extras = {hull_ids, joints} for C4."""
     import constraint_solver_b200 as cs
     from constraint_solver_b200 import scenes
     cube = cs.Polytope.new_cube()
     if workload == "c2":
-        return scenes.c2_perturbed(n_worlds, first_world), [cube], False
-    return scenes.c3_stack(n_worlds, first_world), [cube], True
+        return scenes.c2_perturbed(n_worlds, first_world), [cube], False, {}
+    if workload == "c4":
+        init, hulls, ids, joints = scenes.c4_pile(n_worlds, first_world)
+        return init, hulls, True, {"hull_ids": ids, "joints": joints}
+    return scenes.c3_stack(n_worlds, first_world), [cube], True, {}
 
 
 def cpu_baseline(workload: str, cfg: dict, seconds_target: float = 12.0, dtype=np.float64):
@@ -149,7 +158,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--workload", choices=sorted(WORKLOADS), default=os.environ.get("XPBD_BENCH_WORKLOAD", "c2"))
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default=os.environ.get("XPBD_BENCH_WORKLOAD", DEFAULT_WORKLOAD))
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--worlds", type=int, default=0, help="override worlds per GPU (smaller runs for profiling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -179,12 +188,18 @@ def main():
 
     n_worlds, B, S = cfg["worlds"], cfg["bodies"], cfg["substeps"]
     n_bodies = n_worlds * B
-    init, hulls, body_body = make_scene(args.workload, n_worlds, rank * n_worlds)
+    init, hulls, body_body, extras = make_scene(args.workload, n_worlds, rank * n_worlds)
     dt = 1.0 / 60.0
 
-    w = cs.Worlds(n_worlds, B, device=local_rank, body_body_contacts=body_body)
+    joints = extras.get("joints")
+    w = cs.Worlds(n_worlds, B, device=local_rank, body_body_contacts=body_body,
+                  joints_per_world=0 if joints is None else joints.shape[1])
     for h in hulls:
         w.add_hull(h)
+    if "hull_ids" in extras:
+        w.set_hulls(extras["hull_ids"])
+    if joints is not None:
+        w.set_joints(joints)
     stream = torch.cuda.current_stream()
     w.set_stream(stream.cuda_stream)
     w.upload(init)
@@ -246,6 +261,15 @@ def main():
     e2e_value = world_size * n_bodies * S * args.steps / float(t.item())
     io_bytes = n_bodies * 13 * 4
 
+    # non-FMA FP32 issue peak of this device (FADD/FMUL chains; FMA is off on the whole path for bit parity)
+    fp32_peak = None
+    if rank == 0:
+        import ctypes
+        from constraint_solver_b200 import _abi
+        tf = ctypes.c_double(0.0)
+        if _abi.load().xpbd_fp32_peak_microbench(local_rank, 0, ctypes.byref(tf)) == 0:
+            fp32_peak = tf.value
+
     if rank == 0:
         peaks, peak_kind = measured_peaks()
         avg_launch_s = float(np.mean(launch_ms)) * 1e-3
@@ -266,9 +290,20 @@ def main():
                          "frac": achieved_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_kind,
                          "algorithmic_bytes_per_launch": n_bodies * BYTES_PER_BODY_PER_STEP,
                          "kernel_ms": float(np.mean(launch_ms)),
-                         "note": "all substeps of a frame are fused in registers, so the kernel is FP32-issue/latency bound, not HBM bound (DESIGN.md)"},
+                         "note": "algorithmic bytes = 204 B per body per frame (DESIGN.md section 2); the path is FP32-issue bound, not HBM bound, so this fraction is structurally small (SURVEY.md section 8 row D)"},
             "constraints_last_step": int(constraints),
         }
+        # FP32 side of the roofline (north_star: "achieved fraction of the HBM/FP32 roofline").  Algorithmic flops are
+        # only defined by the reference for its live single-body path: 812 + 364 k per body-substep, k = ground
+        # contacts.  For the multi-body configs see the ncu counters under profiles/.
+        if fp32_peak:
+            fp = {"peak": fp32_peak, "unit": "TFLOP/s", "peak_source": "xpbd_fp32_peak_microbench (non-FMA FADD+FMUL chains), this run"}
+            if args.workload == "c2":
+                flops = 812.0 * n_bodies * S + 364.0 * float(constraints)
+                fp["achieved"] = flops / avg_launch_s / 1e12
+                fp["frac"] = fp["achieved"] / fp32_peak
+                fp["algorithmic_flops_per_launch"] = flops
+            line["roofline"]["fp32"] = fp
         if not args.no_cpu_baseline and world_size == 1:
             try:
                 v, cores, sample, extra = cpu_baseline(args.workload, cfg)

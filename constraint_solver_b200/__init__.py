@@ -11,7 +11,8 @@ from .constraint import Constraint
 from .frame import Frame
 from .geometry import Plane, Polytope, RigidMetrics
 from .rigid import Rigid
-from .world import World, Worlds
+from .world import World, Worlds, shard_range
+from .driver import HeadlessDriver
 
-__all__ = ["Constraint", "Frame", "Plane", "Polytope", "Rigid", "RigidMetrics", "World", "Worlds", "XpbdError",
+__all__ = ["Constraint", "Frame", "Plane", "Polytope", "Rigid", "RigidMetrics", "World", "Worlds", "XpbdError", "HeadlessDriver", "shard_range",
            "collision", "solver", "_abi"]

@@ -37,14 +37,17 @@ constexpr int kEdgeQueueWords = 4 * 64;  // warp-private survivor queue of edge_
 
 // (value, index) arg-max across the warp: larger value wins, equal values -> lower index (the serial scan
 // keeps the FIRST strict maximum), index < 0 = "no candidate".  All lanes receive the result.
+// Two warp reductions (REDUX.SYNC) instead of a 5-round shuffle butterfly: the value is mapped to an unsigned key
+// whose integer order is the float order (never NaN here: `best` is only ever assigned through `distance > best`;
+// -0 is folded into +0 first, which `>` cannot tell apart either), then the lowest index among the lanes that hold
+// the maximum is taken (an index of -1 is the largest unsigned value, so real candidates win).
 XD void warp_argmax_first(float& d, int& i) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        float od = __shfl_xor_sync(0xffffffffu, d, o);
-        int oi = __shfl_xor_sync(0xffffffffu, i, o);
-        bool take = (od > d) || (od == d && oi >= 0 && (i < 0 || oi < i));
-        if (take) { d = od; i = oi; }
-    }
+    const uint32_t u = (uint32_t)__float_as_int(fadd(d, 0.0f));
+    const uint32_t key = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    const uint32_t m = __reduce_max_sync(0xffffffffu, key);
+    const uint32_t idx = __reduce_min_sync(0xffffffffu, key == m ? (uint32_t)i : 0xffffffffu);
+    d = __int_as_float((int)((m & 0x80000000u) ? (m & 0x7fffffffu) : ~m));
+    i = (int)idx;
 }
 
 // collision::face_axes_separation (src/collision.rs:123-149) for hull A's faces against hull B's vertices.
@@ -94,9 +97,8 @@ XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, c
     float4* Q4v = reinterpret_cast<float4*>(Q);
     auto second_half = [&](float4 q) {
         const V3 axis = v3(q.x, q.y, q.z);
-        const int e = __float_as_int(q.w);
-        const int ia = e / nEb;
-        const V3 foot = ld3(WA, T.edge(hA, ia).x);
+        const int e = __float_as_int(q.w);  // ia << 16 | jb: same order as the flat pair index
+        const V3 foot = ld3(WA, T.edge(hA, e >> 16).x);
         const float disp = plane_displacement(foot, axis);
         // plane.distance(B.support(-axis)) = min_v dot(axis, v) - displacement
         float sb = dot(axis, ld3(WB, 0));
@@ -105,10 +107,10 @@ XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, c
         if (distance > best || (distance == best && e < bi)) { best = distance; bi = e; }
     };
     int qn = 0;  // warp-uniform
-    int ia = 0, jb = lane;
+    const int step_a = 32 / nEb, step_b = 32 - step_a * nEb;  // advancing the flat pair index by 32
+    int ia = lane / nEb, jb = lane - ia * nEb;
     for (int e0 = 0; e0 < nPairs; e0 += 32) {
         const int e = e0 + lane;
-        while (jb >= nEb) { jb -= nEb; ++ia; }
         bool pass = false;
         V3 axis = v3(0.f, 0.f, 0.f);
         if (e < nPairs) {
@@ -123,9 +125,10 @@ XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, c
             for (int v = 1; v < nA; ++v) sa = fmaxf(sa, dot(ld3(WA, v), axis));
             pass = !(sa > dot(foot, axis));
         }
-        jb += 32;
         const unsigned m = __ballot_sync(0xffffffffu, pass);
-        if (pass) Q4v[qn + __popc(m & ((1u << lane) - 1u))] = make_float4(axis.x, axis.y, axis.z, __int_as_float(e));
+        if (pass) Q4v[qn + __popc(m & ((1u << lane) - 1u))] = make_float4(axis.x, axis.y, axis.z, __int_as_float((ia << 16) | jb));
+        ia += step_a; jb += step_b;
+        if (jb >= nEb) { jb -= nEb; ++ia; }
         qn += __popc(m);
         __syncwarp();
         if (qn >= 32) {
@@ -138,7 +141,7 @@ XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, c
     __syncwarp();
     warp_argmax_first(best, bi);
     out_d = best;
-    out_pair = bi;
+    out_pair = bi < 0 ? -1 : (bi >> 16) * nEb + (bi & 0xffff);  // flat pair index ia * nEdgesB + jb
 }
 
 // Result of the three queries for one body pair, kept until the per-lane manifold pass.

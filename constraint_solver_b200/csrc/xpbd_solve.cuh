@@ -9,7 +9,7 @@
 // (Rigid::apply_impulse, src/rigid.rs:113-123) of the two bodies are independent; the contact point (3 shuffles)
 // and the inverse mass (1 shuffle) are exchanged inside the pair.  Values the serial specification computes once
 // (depth, lambda, direction) are computed redundantly by both lanes from identical inputs, so every result is
-// bit-identical to the serial evaluation order of oracle/xo_world.hpp.
+// bit-identical to the serial evaluation order of the specification.
 #pragma once
 #include "xpbd_rigid.cuh"
 

@@ -420,8 +420,9 @@ void release_world_scratch(xpbd_batch* b) {
 
 template <class T>
 static cudaError_t dev_alloc(T*& p, size_t n, size_t& total) {
-    total += n * sizeof(T);
-    return cudaMalloc(reinterpret_cast<void**>(&p), n * sizeof(T) ? n * sizeof(T) : 16);
+    const size_t bytes = n * sizeof(T);
+    total += bytes;
+    return cudaMalloc(reinterpret_cast<void**>(&p), bytes > 16 ? bytes : 16);
 }
 
 static int ensure_staged(xpbd_batch* b, StagedState*& out) {

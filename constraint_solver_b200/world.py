@@ -31,6 +31,18 @@ def _quat_from_euler_deg(x: float, y: float, z: float) -> np.ndarray:
     return np.array([qx, qy, qz, s])
 
 
+def shard_range(n_worlds_total: int, rank: int, world_size: int) -> tuple[int, int]:
+    """Contiguous world-index range [first, first + count) owned by `rank`.
+
+    Worlds never interact (src/world.rs:41-42 steps even the two bodies of one world independently), so the
+    batch shards by world index with no collective on the step path.  Remainders go to the lowest ranks."""
+    if world_size <= 0 or not (0 <= rank < world_size) or n_worlds_total < 0:
+        raise ValueError("bad shard arguments")
+    base, rem = divmod(n_worlds_total, world_size)
+    first = rank * base + min(rank, rem)
+    return first, base + (1 if rank < rem else 0)
+
+
 class World:
     """src/world.rs:5-9"""
 

@@ -9,40 +9,50 @@ import oracle_lib as xo
 DT = 1.0 / 60.0
 
 
-def _step_sample(workload, cfg, init38, hull_verts, frames, threads):
-    if workload == "c2":
-        return xo.step_bodies(init38, hull_verts, DT, cfg["substeps"], frames, threads=threads)
-    import oracle_world as xw
-    return xw.step_worlds(init38, cfg["bodies"], hull_verts, DT, cfg["substeps"], frames, threads=threads)
+class _Sample:
+    """A bounded sample of a workload, prepared like the GPU arm (same scene generator, same pre-roll)."""
 
+    def __init__(self, workload, cfg, n_worlds, dtype, make_scene, threads):
+        init, hulls, _, extras = make_scene(workload, n_worlds, 0)
+        self.workload, self.cfg, self.threads = workload, cfg, threads
+        self.r = xo.rigid38(init).astype(dtype)
+        self.hulls, self.extras = hulls, extras
+        self.n_worlds = n_worlds
+        self.step(cfg["preroll"])  # contact-active state, as on the GPU
 
-def _prepare(workload, cfg, n_worlds, dtype, make_scene, threads):
-    init, hulls, _ = make_scene(workload, n_worlds, 0)
-    r = xo.rigid38(init).astype(dtype)
-    verts = hulls[0].vertices
-    # same pre-roll as the GPU arm so the timed frames are contact-active
-    _step_sample(workload, cfg, r, verts, cfg["preroll"], threads)
-    return r, verts
+    def step(self, frames, threads=None):
+        threads = threads or self.threads
+        if not frames:
+            return
+        if self.workload == "c2":
+            xo.step_bodies(self.r, self.hulls[0].vertices, DT, self.cfg["substeps"], frames, threads=threads)
+        else:
+            import oracle_world as xw
+            xw.step_worlds(self.r, self.cfg["bodies"], list(self.hulls), DT, self.cfg["substeps"], frames, threads=threads,
+                           hull_ids=self.extras.get("hull_ids"), joints=self.extras.get("joints"))
 
 
 def time_oracle(workload, cfg, seconds_target, dtype, make_scene):
     """Returns (body-substeps/s, cores, sample description, extra dict)."""
     threads = xo.hardware_threads()
     B, S = cfg["bodies"], cfg["substeps"]
-    n_worlds = max(threads * 8, 4096 // B)
+    n_worlds = max(threads * 8, 4096 // B) if B <= 16 else threads * 2
     out = {}
+    sample = ""
     for name, dt_ in (("f64", np.float64), ("f32", np.float32)):
-        r, verts = _prepare(workload, cfg, n_worlds, dt_, make_scene, threads)
-        t0 = time.perf_counter(); _step_sample(workload, cfg, r, verts, 1, threads); probe = time.perf_counter() - t0
+        smp = _Sample(workload, cfg, n_worlds, dt_, make_scene, threads)
+        t0 = time.perf_counter(); smp.step(1); probe = time.perf_counter() - t0
         frames = int(max(1, min(200, (seconds_target / 2) / max(probe, 1e-6))))
-        t0 = time.perf_counter(); _step_sample(workload, cfg, r, verts, frames, threads); el = time.perf_counter() - t0
+        t0 = time.perf_counter(); smp.step(frames); el = time.perf_counter() - t0
         out[name] = n_worlds * B * S * frames / el
-        sample = f"{n_worlds} worlds x {B} bodies x {frames} frames x {S} substeps after {cfg['preroll']} pre-roll frames, oracle port, {threads} threads"
+        sample = (f"{n_worlds} worlds x {B} bodies x {frames} frames x {S} substeps after {cfg['preroll']} pre-roll frames, "
+                  f"oracle port, {threads} threads")
     # single thread, f64
-    r, verts = _prepare(workload, cfg, max(64 // B, 8), np.float64, make_scene, threads)
-    nw1 = len(r) // B
-    t0 = time.perf_counter(); _step_sample(workload, cfg, r, verts, 20, 1); el = time.perf_counter() - t0
-    one = nw1 * B * S * 20 / el
+    nw1 = max(64 // B, 8) if B <= 16 else 2
+    smp = _Sample(workload, cfg, nw1, np.float64, make_scene, threads)
+    f1 = 20 if B <= 16 else 3
+    t0 = time.perf_counter(); smp.step(f1, threads=1); el = time.perf_counter() - t0
+    one = nw1 * B * S * f1 / el
     return out["f64"], threads, sample, {"value_f32": out["f32"], "value_f64_1thread": one, "precision": "f64 (the reference's)"}
 
 
@@ -50,13 +60,15 @@ def run_reference_arm(workload, cfg, steps, warmup, make_scene):
     """bench.py --impl reference: each step = one frame of a bounded sample, f64, all host threads."""
     threads = xo.hardware_threads()
     B, S = cfg["bodies"], cfg["substeps"]
-    n_worlds = max(threads * 64, 16384 // B)
-    r, verts = _prepare(workload, cfg, n_worlds, np.float64, make_scene, threads)
+    n_worlds = max(threads * 64, 16384 // B) if B <= 16 else threads * 4
+    if workload != "c2":
+        n_worlds = max(threads * 8, n_worlds // 8)  # multi-body worlds cost ~100x more per body-substep
+    smp = _Sample(workload, cfg, n_worlds, np.float64, make_scene, threads)
     for _ in range(warmup):
-        _step_sample(workload, cfg, r, verts, 1, threads)
+        smp.step(1)
     t0 = time.perf_counter()
     for _ in range(steps):
-        _step_sample(workload, cfg, r, verts, 1, threads)
+        smp.step(1)
     el = time.perf_counter() - t0
     return {"value": n_worlds * B * S * steps / el, "ms_per_step": el / steps * 1e3, "cores": threads,
             "sample": f"{n_worlds} worlds x {B} bodies per step (bounded sample of the workload), f64 oracle port, {threads} threads"}

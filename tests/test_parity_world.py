@@ -174,3 +174,24 @@ def test_c3_full_size_properties_and_sampled_parity():
     idx = np.arange(0, n, 1563)
     cpu, _ = _run_cpu(init[idx], [CUBE], frames, 20)
     assert np.array_equal(g[idx].reshape(-1, 38), cpu.astype(np.float64))
+
+
+def test_c4_pile_mixed_quickhull_hulls_with_joints():
+    """C4 (BASELINE.json configs[3]) at reduced world count: 64 bodies per world drawn from the reference's built-ins
+    and QuickHull hulls, 32 distance joints per world; every world compared with the oracle."""
+    init, hulls, ids, joints = scenes.c4_pile(24)
+    gpu, c = _check(init, hulls, 30, 20, hull_ids=ids, joints=joints)
+    g = xo.rigid38(gpu)
+    assert np.isfinite(g).all()
+    assert c["manifolds"] > 0 and c["constraints"] > 24 * 32 * 30 * 20  # joints alone give that many
+    assert g.reshape(24, 64, 38)[:, :, 33].min() > -0.5  # nothing fell through the ground
+
+
+def test_c4_shard_equals_slice_of_the_whole():
+    """Sharding by world index: stepping worlds [8, 16) alone gives the same bits as stepping
+    them inside the whole batch."""
+    init, hulls, ids, joints = scenes.c4_pile(16)
+    whole, _ = _run_gpu(init, hulls, 6, 20, hull_ids=ids, joints=joints)
+    init2, _, ids2, joints2 = scenes.c4_pile(8, first_world=8)
+    part, _ = _run_gpu(init2, hulls, 6, 20, hull_ids=ids2, joints=joints2)
+    assert np.array_equal(xo.rigid38(whole[8:]), xo.rigid38(part))
