@@ -20,6 +20,8 @@ XD float fsub(float a, float b) { return __fsub_rn(a, b); }
 XD float fmul(float a, float b) { return __fmul_rn(a, b); }
 XD float fdiv(float a, float b) { return __fdiv_rn(a, b); }
 XD float fsqrt(float a) { return __fsqrt_rn(a); }
+// 1/x, correctly rounded: the same bits as fdiv(1.0f, x) (both are the RN rounding of the same real number), fewer instructions
+XD float frcp(float a) { return __frcp_rn(a); }
 
 struct V3 {
     float x, y, z;
@@ -49,7 +51,7 @@ XD V3 cross(V3 a, V3 b) {
 }
 XD float magnitude2(V3 a) { return dot(a, a); }
 XD float magnitude(V3 a) { return fsqrt(dot(a, a)); }
-XD V3 normalize(V3 a) { return a * fdiv(1.0f, magnitude(a)); }
+XD V3 normalize(V3 a) { return a * frcp(magnitude(a)); }
 XD V3 project_on(V3 a, V3 other) { return other * fdiv(dot(a, other), magnitude2(other)); }
 
 XD Q4 q4(float s, float x, float y, float z) { Q4 q; q.x = x; q.y = y; q.z = z; q.s = s; return q; }
@@ -73,7 +75,7 @@ XD V3 operator*(Q4 q, V3 r) {
     return (cross(v, tmp) * 2.0f) + r;
 }
 XD float qdot(Q4 a, Q4 b) { return fadd(fmul(a.s, b.s), dot(qv(a), qv(b))); }
-XD Q4 qnormalize(Q4 q) { return q * fdiv(1.0f, fsqrt(qdot(q, q))); }
+XD Q4 qnormalize(Q4 q) { return q * frcp(fsqrt(qdot(q, q))); }
 
 XD M3 operator*(float k, M3 m) { M3 o; o.c0 = k * m.c0; o.c1 = k * m.c1; o.c2 = k * m.c2; return o; }
 // Matrix3 * Vector3: rows dotted with v.

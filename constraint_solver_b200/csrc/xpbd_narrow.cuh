@@ -50,21 +50,69 @@ XD void warp_argmax_first(float& d, int& i) {
     i = (int)idx;
 }
 
+// Support scans: extreme value of dot(axis, v) over the first n vertices of a float4 vertex array.  The common hull
+// sizes (tetrahedron 4, cube 8, icosahedron 12) get fully unrolled instantiations — no loop control, FMNMX3 pairs —
+// chosen by a warp-uniform switch; any other size takes the rolled loop.  min/max are exact, so the order in which
+// they are folded cannot change the value.
+template <int NV, bool kMax>
+XD float scan_dots_t(const float* W, int n, V3 axis) {
+    float s = dot(axis, ld3(W, 0));
+    if (NV > 0) {
+#pragma unroll
+        for (int v = 1; v < NV; ++v) { const float d = dot(axis, ld3(W, v)); s = kMax ? fmaxf(s, d) : fminf(s, d); }
+    } else {
+        for (int v = 1; v < n; ++v) { const float d = dot(axis, ld3(W, v)); s = kMax ? fmaxf(s, d) : fminf(s, d); }
+    }
+    return s;
+}
+template <bool kMax>
+XD float scan_dots(const float* W, int n, V3 axis) {
+    switch (n) {
+        case 4: return scan_dots_t<4, kMax>(W, n, axis);
+        case 8: return scan_dots_t<8, kMax>(W, n, axis);
+        case 12: return scan_dots_t<12, kMax>(W, n, axis);
+        default: return scan_dots_t<0, kMax>(W, n, axis);
+    }
+}
+
 // collision::face_axes_separation (src/collision.rs:123-149) for hull A's faces against hull B's vertices.
-// L: warp-private scratch for B's vertices in A-local space (3 floats per vertex).
+// L: warp-private scratch for B's vertices in A-local space (float4 per vertex).
+// Lanes are spread over (face, vertex chunk): with nF <= 16 faces, G = 32 / pow2(nF) lane groups each scan every
+// G-th vertex and a shuffle-min butterfly across the groups completes the support value of every face
+// (cube vs cube: 4 groups x 2 vertices instead of 6 active lanes x 8 vertices).
 XD void face_query(const HullTable& T, const HullDesc& hA, const Fr& FinvA, const float* WB, int nB, float* L, int lane,
                    float& out_d, int& out_face) {
     for (int v = lane; v < nB; v += 32) st3(L, v, FinvA * ld3(WB, v));  // frames.0.inverse() * (frames.1 * p)
     __syncwarp();
     float best = -FLT_MAX;  // f64::MIN
     int bi = -1;            // usize::MAX
-    for (int f = lane; f < hA.n_faces; f += 32) {
-        const float4 pl = T.plane(hA, f);
-        const V3 n = v3(pl.x, pl.y, pl.z);
-        float m = dot(n, ld3(L, 0));
-        for (int v = 1; v < nB; ++v) m = fminf(m, dot(n, ld3(L, v)));
-        const float distance = fsub(m, pl.w);  // plane.distance(support)
-        if (distance > best) { best = distance; bi = f; }
+    const int nF = hA.n_faces;
+    int nFp = 4;
+    while (nFp < nF && nFp < 32) nFp <<= 1;
+    int G = 32 / nFp;                 // lane groups
+    while (G > nB) G >>= 1;           // every group must own at least one vertex
+    if (G > 1) {
+        const int f = lane & (nFp - 1), g = lane / nFp;
+        float m = 0.0f;
+        float4 pl = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (f < nF && g < G) {
+            pl = T.plane(hA, f);
+            const V3 n = v3(pl.x, pl.y, pl.z);
+            m = dot(n, ld3(L, g));
+            for (int v = g + G; v < nB; v += G) m = fminf(m, dot(n, ld3(L, v)));
+        }
+        for (int o = nFp; o < nFp * G; o <<= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (f < nF && g == 0) {
+            const float distance = fsub(m, pl.w);  // plane.distance(support)
+            if (distance > best) { best = distance; bi = f; }
+        }
+    } else {
+        for (int f = lane; f < nF; f += 32) {
+            const float4 pl = T.plane(hA, f);
+            const float m = scan_dots<false>(L, nB, v3(pl.x, pl.y, pl.z));
+            const float distance = fsub(m, pl.w);
+            if (distance > best) { best = distance; bi = f; }
+        }
     }
     warp_argmax_first(best, bi);
     out_d = best;
@@ -101,8 +149,7 @@ XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, c
         const V3 foot = ld3(WA, T.edge(hA, e >> 16).x);
         const float disp = plane_displacement(foot, axis);
         // plane.distance(B.support(-axis)) = min_v dot(axis, v) - displacement
-        float sb = dot(axis, ld3(WB, 0));
-        for (int v = 1; v < nB; ++v) sb = fminf(sb, dot(axis, ld3(WB, v)));
+        const float sb = scan_dots<false>(WB, nB, axis);
         const float distance = fsub(sb, disp);
         if (distance > best || (distance == best && e < bi)) { best = distance; bi = e; }
     };
@@ -121,8 +168,7 @@ XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, c
             axis = normalize(cross(edge_a, edge_b));  // parallel edges -> NaN axis, no guard (as the reference)
             if (dot(axis, foot - CA) < 0.0f) axis = -axis;
             // Ignore if another point on `a` is further in the direction to `b`.
-            float sa = dot(ld3(WA, 0), axis);
-            for (int v = 1; v < nA; ++v) sa = fmaxf(sa, dot(ld3(WA, v), axis));
+            const float sa = scan_dots<true>(WA, nA, axis);  // dot(v, axis) == dot(axis, v): IEEE multiplication commutes
             pass = !(sa > dot(foot, axis));
         }
         const unsigned m = __ballot_sync(0xffffffffu, pass);

@@ -125,7 +125,7 @@ __global__ void solve_kernel(double* rigids, int64_t n, const double* cons, cons
         const V3 c0 = v3(f32(q[1]), f32(q[2]), f32(q[3])), c1 = v3(f32(q[4]), f32(q[5]), f32(q[6]));
         const V3 diff = c1 - c0;
         const float dist = magnitude(diff);
-        const V3 dir = diff * fdiv(1.0f, dist);
+        const V3 dir = diff * frcp(dist);
         const float w = inverse_resistance(d.position, d.rotation, k.inverse_mass, k.inverse_inertia, k.center_of_mass, c0, dir);
         const float lambda = fdiv(fsub(dist, f32(q[7])), fadd(w, compliance));
         rigid_apply_impulse(d.position, d.rotation, k.inverse_mass, k.inverse_inertia, k.center_of_mass, lambda * dir, c0);

@@ -47,7 +47,7 @@ XD void ground_contact(BodyDyn& d, const BodyConst& k, const Fr& frame_inv, cons
     // solver::solve body (src/solver.rs:22-26), Constraint methods (src/constraint.rs:13-37)
     V3 diff = c1 - p;
     float dist = magnitude(diff);                  // current_distance(); distance == 0
-    V3 dir = diff * fdiv(1.0f, dist);              // direction() = normalize
+    V3 dir = diff * frcp(dist);              // direction() = normalize
     float w = inverse_resistance(d.position, d.rotation, k.inverse_mass, k.inverse_inertia, k.center_of_mass, p, dir);
     float lambda = fdiv(fsub(dist, 0.0f), fadd(w, compliance));
     rigid_apply_impulse(d.position, d.rotation, k.inverse_mass, k.inverse_inertia, k.center_of_mass, lambda * dir, p);

@@ -66,7 +66,7 @@ XD void solve_joint(Acc& A, int side, unsigned pm, int me, bool two_body, V3 anc
     const V3 diff = side ? p_me - p_ot : p_ot - p_me;  // pb - pa
     const float dist = magnitude(diff);
     if (dist == 0.0f) return;
-    const V3 dir = diff * fdiv(1.0f, dist);
+    const V3 dir = diff * frcp(dist);
     const float w_me = me >= 0 ? acc_inverse_resistance(A, me, p_me, dir) : 0.0f;
     const float w_ot = swap1(w_me, pm);
     const float w_a = side ? w_ot : w_me, w_b = side ? w_me : w_ot;
@@ -101,7 +101,7 @@ XD void velocity_contact(Acc& A, int side, unsigned pm, int me, V3 anchor, V3 n,
     const V3 dv = -(vnormal + vt * friction);
     const float mag = magnitude(dv);
     if (!(mag > 0.0f)) return;
-    const V3 dir = dv * fdiv(1.0f, mag);
+    const V3 dir = dv * frcp(mag);
     const float res_me = acc_inverse_resistance(A, me, p_me, dir);
     const float resistance = fadd(res_me, swap1(res_me, pm));
     const V3 p = dir * fdiv(mag, resistance);

@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(256) stage_prepare_kernel(StagedParams P) {
                         const V3 c1 = target - P.friction * delta_t;
                         const V3 diff = c1 - p;
                         const float dist = magnitude(diff);
-                        const V3 dir = diff * fdiv(1.0f, dist);
+                        const V3 dir = diff * frcp(dist);
                         float4* c = reinterpret_cast<float4*>(gc + (size_t)idx * kGroundWords);
                         c[0] = make_float4(__int_as_float(cons_head(kGround, b, -1)), p.x, p.y, p.z);
                         c[1] = make_float4(dir.x, dir.y, dir.z, dist);
@@ -330,6 +330,57 @@ struct GlobalBodies {  // body accessor over the SoA arrays in HBM/L2; g0 = firs
     }
 };
 
+// One body held in registers by a solver lane.  A manifold applies up to four contacts to the same two bodies in
+// a row, and each contact reads the body ~3 times: caching turns ~12 dependent L2 round trips per contact into one
+// load when the lane's body changes.  Protocol inside a lane pair, per constraint (`me` = the body this lane
+// needs, -1 = none):   release(me);  __syncwarp(pm);  acquire(me);
+// A lane writes its dirty body back BEFORE the barrier whenever it moves on to another body, so the other lane
+// — which can only need that body after the owner left it (a constraint never has body a == body b) — always
+// reads current state.  kVel = false: sweep (pose is written; velocity.x rides along in dynA);
+// kVel = true: velocity pass (pose is read-only, velocities are written).
+template <bool kVel>
+struct CachedBody {
+    const BodyArrays& A;
+    int64_t g0;
+    int cur = -1;
+    bool dirty = false;
+    float4 a4, b4, c4;  // dynA, dynB, dynC
+    float d1;           // dynD
+    float invm_; V3 com_; M3 I_;
+    XD void release(int me) {
+        if (cur >= 0 && cur != me) {
+            if (dirty) {
+                const int64_t g = g0 + cur;
+                A.dynA[g] = a4;
+                if (kVel) { A.dynB[g] = b4; A.dynD[g] = d1; } else { A.dynC[g] = c4; }
+            }
+            cur = -1; dirty = false;
+        }
+    }
+    XD void acquire(int me) {
+        if (me >= 0 && cur != me) {
+            const int64_t g = g0 + me;
+            a4 = A.dynA[g]; c4 = A.dynC[g];
+            if (kVel) { b4 = A.dynB[g]; d1 = A.dynD[g]; }
+            const float4 k0 = __ldg(&A.k0[g]), p = __ldg(&A.k1[g]), q = __ldg(&A.k2[g]), r = __ldg(&A.k3[g]);
+            invm_ = k0.x; com_ = v3(k0.y, k0.z, k0.w);
+            I_.c0 = v3(p.x, p.y, p.z); I_.c1 = v3(p.w, q.x, q.y); I_.c2 = v3(q.z, q.w, r.x);
+            cur = me; dirty = false;
+        }
+    }
+    XD void flush() { release(-2); }
+    // accessor interface of xpbd_solve.cuh (always called with b == cur)
+    XD V3 pos(int) const { return v3(a4.x, a4.y, a4.z); }
+    XD Q4 rot(int) const { return q4(c4.w, c4.x, c4.y, c4.z); }
+    XD V3 com(int) const { return com_; }
+    XD float invm(int) const { return invm_; }
+    XD M3 inertia(int) const { return I_; }
+    XD V3 vel(int) const { return v3(a4.w, b4.x, b4.y); }
+    XD V3 ang(int) const { return v3(b4.z, b4.w, d1); }
+    XD void set_pose(int, V3 p, Q4 q) { a4 = make_float4(p.x, p.y, p.z, a4.w); c4 = make_float4(q.x, q.y, q.z, q.s); dirty = true; }
+    XD void set_vel(int, V3 v, V3 w) { a4.w = v.x; b4 = make_float4(v.y, v.z, w.x, w.y); d1 = w.z; dirty = true; }
+};
+
 __global__ void __launch_bounds__(128) stage_solve_kernel(StagedParams P) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t world = t >> 1;
@@ -338,60 +389,71 @@ __global__ void __launch_bounds__(128) stage_solve_kernel(StagedParams P) {
     unsigned applied = 0;
     if (blockIdx.x == 0 && threadIdx.x == 0) *P.S.work_count = 0;  // consumed by sat + manifold; next substep appends again
     if (world < P.n_worlds) {
-        GlobalBodies A{P.bodies, P.S.ppos, P.S.prot, world * P.B};
         const StepConsts sc = P.sc;
         const int n_ground = P.S.n_ground[world], n_pairs = P.S.n_pairs[world];
-        // --- sweep: ground constraints (body-major, hull-vertex order) ...
-        const float4* gc = reinterpret_cast<const float4*>(P.S.gcons + (size_t)world * P.S.capG * kGroundWords);
-        for (int k = 0; k < n_ground; ++k) {
-            __syncwarp(pm);
-            if (side == 0) {
-                const float4 c0 = gc[2 * k], c1 = gc[2 * k + 1];
-                solve_ground(A, head_a(__float_as_int(c0.x)), v3(c0.y, c0.z, c0.w), v3(c1.x, c1.y, c1.z), c1.w, sc);
-            }
-        }
-        applied += n_ground;
-        // --- ... then the manifolds of the candidate pairs i<j in lexicographic order ...
         int4* pairs = P.S.pairs + (size_t)world * P.S.capP;
         float4* pc = P.S.pcons + (size_t)world * P.S.capP * kMaxManifold * 3;
-        for (int p = 0; p < n_pairs; ++p) {
-            const int cnt = pairs[p].w;
-            for (int k = 0; k < cnt; ++k) {
-                __syncwarp(pm);
-                float4* c = pc + ((size_t)p * kMaxManifold + k) * 3;
-                const float4 c0 = c[0], c1 = c[1], c2 = c[2];
-                const int head = __float_as_int(c0.x);
-                const bool active = solve_contact(A, side, pm, side ? head_b(head) : head_a(head),
-                                                  side ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w), v3(c2.x, c2.y, c2.z), sc);
-                if (active && side == 0) c[0].x = __int_as_float(head | kActiveBit);
+        {
+            CachedBody<false> C{P.bodies, world * P.B};
+            // --- sweep: ground constraints (body-major, hull-vertex order) ...
+            const float4* gc = reinterpret_cast<const float4*>(P.S.gcons + (size_t)world * P.S.capG * kGroundWords);
+            for (int k = 0; k < n_ground; ++k) {
+                const float4 c0 = gc[2 * k], c1 = gc[2 * k + 1];
+                const int me = side ? -1 : head_a(__float_as_int(c0.x));
+                C.release(me); __syncwarp(pm); C.acquire(me);
+                if (side == 0) solve_ground(C, me, v3(c0.y, c0.z, c0.w), v3(c1.x, c1.y, c1.z), c1.w, sc);
             }
-            applied += cnt;
-        }
-        // --- ... then the joints in index order
-        for (int jn = 0; jn < P.J; ++jn) {
-            const DeviceJoint q = P.joints[world * P.J + jn];
-            if (q.body_a < 0) continue;
-            __syncwarp(pm);
-            solve_joint(A, side, pm, side ? q.body_b : q.body_a, q.body_b >= 0, side ? v3(q.bx, q.by, q.bz) : v3(q.ax, q.ay, q.az),
-                        q.distance, sc);
-            ++applied;
+            applied += n_ground;
+            // --- ... then the manifolds of the candidate pairs i<j in lexicographic order ...
+            for (int p = 0; p < n_pairs; ++p) {
+                const int cnt = pairs[p].w;
+                for (int k = 0; k < cnt; ++k) {
+                    float4* c = pc + ((size_t)p * kMaxManifold + k) * 3;
+                    const float4 c0 = c[0], c1 = c[1], c2 = c[2];
+                    const int head = __float_as_int(c0.x);
+                    const int me = side ? head_b(head) : head_a(head);
+                    C.release(me); __syncwarp(pm); C.acquire(me);
+                    const bool active = solve_contact(C, side, pm, me, side ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w),
+                                                      v3(c2.x, c2.y, c2.z), sc);
+                    if (active && side == 0) c[0].x = __int_as_float(head | kActiveBit);
+                }
+                applied += cnt;
+            }
+            // --- ... then the joints in index order
+            for (int jn = 0; jn < P.J; ++jn) {
+                const DeviceJoint q = P.joints[world * P.J + jn];
+                if (q.body_a < 0) continue;
+                const int me = side ? q.body_b : q.body_a;
+                C.release(me); __syncwarp(pm); C.acquire(me);
+                solve_joint(C, side, pm, me, q.body_b >= 0, side ? v3(q.bx, q.by, q.bz) : v3(q.ax, q.ay, q.az), q.distance, sc);
+                ++applied;
+            }
+            C.flush();
         }
         __syncwarp(pm);
         // --- Rigid::derive, bodies split between the two lanes
-        for (int b = side; b < P.B; b += 2) derive_body(A, b, sc.dt);
+        {
+            GlobalBodies A{P.bodies, P.S.ppos, P.S.prot, world * P.B};
+            for (int b = side; b < P.B; b += 2) derive_body(A, b, sc.dt);
+        }
         // --- velocity pass over the contacts that were active in the sweep
-        for (int p = 0; p < n_pairs; ++p) {
-            const int cnt = pairs[p].w;
-            for (int k = 0; k < cnt; ++k) {
-                __syncwarp(pm);
-                const float4* c = pc + ((size_t)p * kMaxManifold + k) * 3;
-                const float4 c0 = c[0];
-                const int head = __float_as_int(c0.x);
-                if (!(head & kActiveBit)) continue;
-                const float4 c1 = c[1], c2 = c[2];
-                velocity_contact(A, side, pm, side ? head_b(head) : head_a(head),
-                                 side ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w), v3(c2.x, c2.y, c2.z), P.friction);
+        {
+            CachedBody<true> C{P.bodies, world * P.B};
+            for (int p = 0; p < n_pairs; ++p) {
+                const int cnt = pairs[p].w;
+                for (int k = 0; k < cnt; ++k) {
+                    const float4* c = pc + ((size_t)p * kMaxManifold + k) * 3;
+                    const float4 c0 = c[0];
+                    const int head = __float_as_int(c0.x);
+                    if (!(head & kActiveBit)) continue;
+                    const float4 c1 = c[1], c2 = c[2];
+                    const int me = side ? head_b(head) : head_a(head);
+                    C.release(me); __syncwarp(pm); C.acquire(me);
+                    velocity_contact(C, side, pm, me, side ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w), v3(c2.x, c2.y, c2.z),
+                                     P.friction);
+                }
             }
+            C.flush();
         }
         if (side) applied = 0;
     }

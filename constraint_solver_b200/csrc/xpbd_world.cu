@@ -110,7 +110,7 @@ XD int phase_vertices_ground(float* R, float* S, const WorldLayout& L, const Hul
                 const V3 c1 = target - friction * delta_t;
                 const V3 diff = c1 - p;
                 const float dist = magnitude(diff);
-                const V3 dir = diff * fdiv(1.0f, dist);
+                const V3 dir = diff * frcp(dist);
                 float* c = R + L.cons + kConsWords * idx;
                 reinterpret_cast<int*>(c)[0] = cons_head(kGround, b, -1);
                 c[1] = p.x; c[2] = p.y; c[3] = p.z; c[4] = dir.x; c[5] = dir.y; c[6] = dir.z; c[7] = dist;
