@@ -250,6 +250,17 @@ def main():
     launch_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
     stats = w.stats()
     constraints = stats["constraints"]
+    # per-stage device times of the staged multi-body pipeline (CUDA events on the batch stream around each kernel of
+    # the last substep of a step call; xpbd_step_stats.stage_ms), averaged over a few extra untimed step calls
+    stage_ms, cand_pairs = None, 0
+    if stats["kernel_launches"] > 1:
+        acc = np.zeros(4)
+        for _ in range(5):
+            w.integrate(dt, S, 1, sync=True)
+            st_ = w.stats()
+            acc += np.array(st_["stage_ms"])
+            cand_pairs = int(st_["candidate_pairs"])
+        stage_ms = (acc / 5).tolist()
     t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
     if world_size > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -324,6 +335,27 @@ def main():
                 fp["frac"] = fp["achieved"] / fp32_peak
                 fp["algorithmic_flops_per_launch"] = flops
             line["roofline"]["fp32"] = fp
+        if stage_ms is not None and stage_ms[1] > 0:
+            # Dominant kernel of the multi-body pipeline: stage_sat_kernel (one warp per candidate body pair).
+            # Algorithmic bytes per pair: world-space vertices of both hulls (12 B each), two rotations (16 B each), two
+            # inverse-frame positions and the centroid of A (12 B each), the pair record (16 B read + 8 B written).
+            mean_verts = float(np.mean([len(h.vertices) for h in hulls])) if "hull_ids" not in extras else \
+                float(np.mean(np.array([len(h.vertices) for h in hulls])[extras["hull_ids"]]))
+            bytes_per_pair = 2 * 12.0 * mean_verts + 2 * 16 + 3 * 12 + 24
+            sat_gbs = cand_pairs * bytes_per_pair / (stage_ms[1] * 1e-3) / 1e9
+            line["roofline"] = {
+                "bound": "hbm", "kernel": "stage_sat_kernel", "achieved": sat_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "frac": sat_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_kind,
+                "algorithmic_bytes_per_launch": cand_pairs * bytes_per_pair, "kernel_ms": stage_ms[1],
+                "candidate_pairs_per_launch": cand_pairs, "bytes_per_pair": bytes_per_pair,
+                "stage_ms": dict(zip(["prepare", "sat", "manifold", "solve"], stage_ms)),
+                "share_of_step": stage_ms[1] / max(sum(stage_ms), 1e-9),
+                "step": line["roofline"],
+                "note": "dominant kernel of the staged pipeline, timed with CUDA events on the batch stream inside the library; "
+                        "FP32-issue bound (673 FP instructions of 1.8k per pair, DESIGN.md section 5), so the HBM fraction is small by construction",
+            }
+            if "fp32" in line["roofline"]["step"]:
+                line["roofline"]["fp32"] = line["roofline"]["step"].pop("fp32")
         if not args.no_cpu_baseline and world_size == 1:
             try:
                 v, cores, sample, extra = cpu_baseline(args.workload, cfg)

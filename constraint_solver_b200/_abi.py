@@ -85,6 +85,8 @@ class StepStatsC(C.Structure):
         ("overflow_worlds", C.c_uint64),
         ("elapsed_ms", C.c_float),
         ("kernel_launches", C.c_int32),
+        ("stage_ms", C.c_float * 4),
+        ("candidate_pairs", C.c_uint64),
     ]
 
 

@@ -105,6 +105,7 @@ int xpbd_batch_create(const xpbd_batch_desc* desc, xpbd_batch** out) {
     std::memset(b->h_counters, 0, 4 * sizeof(unsigned long long));
     TRY_OR_BAIL(cudaEventCreate(&b->ev_start));
     TRY_OR_BAIL(cudaEventCreate(&b->ev_stop));
+    for (int k = 0; k < 5; ++k) TRY_OR_BAIL(cudaEventCreate(&b->ev_stage[k]));
     if (desc->joints_per_world > 0) {
         const size_t jb = (size_t)desc->n_worlds * desc->joints_per_world * sizeof(DeviceJoint);
         TRY_OR_BAIL(cudaMalloc(&b->d_joints, jb));
@@ -134,6 +135,7 @@ int xpbd_batch_destroy(xpbd_batch* b) {
     if (b->h_counters) cudaFreeHost(b->h_counters);
     if (b->ev_start) cudaEventDestroy(b->ev_start);
     if (b->ev_stop) cudaEventDestroy(b->ev_stop);
+    for (int k = 0; k < 5; ++k) if (b->ev_stage[k]) cudaEventDestroy(b->ev_stage[k]);
     if (b->own_stream && b->stream) cudaStreamDestroy(b->stream);
     delete b;
     return XPBD_OK;
@@ -314,6 +316,7 @@ int xpbd_batch_step(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_f
     if (int rc = finalize_hulls(b)) return rc;
     XPBD_CUDA_TRY(cudaEventRecord(b->ev_start, b->stream));
     XPBD_CUDA_TRY(cudaMemsetAsync(b->d_counters, 0, 4 * sizeof(unsigned long long), b->stream));
+    b->stage_timed = false;
     const bool world_path = b->desc.body_body_contacts != 0 || b->desc.joints_per_world > 0;
     int rc = world_path ? step_world(b, (float)dt, substep_count, n_frames)
                         : step_single(b, (float)dt, substep_count, n_frames);
@@ -344,6 +347,11 @@ int xpbd_batch_last_stats(xpbd_batch* b, xpbd_step_stats* out) {
     b->last.elapsed_ms = ms;
     b->last.constraints = b->h_counters[0];
     b->last.overflow_worlds = b->h_counters[1];
+    b->last.candidate_pairs = b->stage_timed ? b->h_counters[3] : 0;
+    for (int k = 0; k < 4; ++k) {
+        b->last.stage_ms[k] = 0.f;
+        if (b->stage_timed) XPBD_CUDA_TRY(cudaEventElapsedTime(&b->last.stage_ms[k], b->ev_stage[k], b->ev_stage[k + 1]));
+    }
     if (b->h_counters[2]) set_error("TMA hull staging fell back to plain loads in %llu blocks", b->h_counters[2]);
     *out = b->last;
     return XPBD_OK;

@@ -101,6 +101,8 @@ struct xpbd_batch {
     unsigned long long* d_counters = nullptr;  // [0] constraints, [1] overflow worlds, [2] tma fallbacks
     unsigned long long* h_counters = nullptr;  // pinned
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    cudaEvent_t ev_stage[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // staged pipeline: around the last substep's kernels
+    bool stage_timed = false;
     xpbd_step_stats last{};
     bool stepped = false;
     void* world_scratch = nullptr;  // owned by the multi-body path

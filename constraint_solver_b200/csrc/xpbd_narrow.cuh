@@ -80,13 +80,15 @@ XD float scan_dots(const float* W, int n, V3 axis) {
 // Lanes are spread over (face, vertex chunk): with nF <= 16 faces, G = 32 / pow2(nF) lane groups each scan every
 // G-th vertex and a shuffle-min butterfly across the groups completes the support value of every face
 // (cube vs cube: 4 groups x 2 vertices instead of 6 active lanes x 8 vertices).
-XD void face_query(const HullTable& T, const HullDesc& hA, const Fr& FinvA, const float* WB, int nB, float* L, int lane,
-                   float& out_d, int& out_face) {
+// NF / NB > 0: face / vertex counts known at compile time (the cube-cube instantiation), 0: taken from nF / nB.
+template <int NF, int NB>
+XD void face_query_t(const float4* planes, int nF_rt, const Fr& FinvA, const float* WB, int nB_rt, float* L, int lane,
+                     float& out_d, int& out_face) {
+    const int nF = NF ? NF : nF_rt, nB = NB ? NB : nB_rt;
     for (int v = lane; v < nB; v += 32) st3(L, v, FinvA * ld3(WB, v));  // frames.0.inverse() * (frames.1 * p)
     __syncwarp();
     float best = -FLT_MAX;  // f64::MIN
     int bi = -1;            // usize::MAX
-    const int nF = hA.n_faces;
     int nFp = 4;
     while (nFp < nF && nFp < 32) nFp <<= 1;
     int G = 32 / nFp;                 // lane groups
@@ -96,7 +98,7 @@ XD void face_query(const HullTable& T, const HullDesc& hA, const Fr& FinvA, cons
         float m = 0.0f;
         float4 pl = make_float4(0.f, 0.f, 0.f, 0.f);
         if (f < nF && g < G) {
-            pl = T.plane(hA, f);
+            pl = planes[f];
             const V3 n = v3(pl.x, pl.y, pl.z);
             m = dot(n, ld3(L, g));
             for (int v = g + G; v < nB; v += G) m = fminf(m, dot(n, ld3(L, v)));
@@ -108,7 +110,7 @@ XD void face_query(const HullTable& T, const HullDesc& hA, const Fr& FinvA, cons
         }
     } else {
         for (int f = lane; f < nF; f += 32) {
-            const float4 pl = T.plane(hA, f);
+            const float4 pl = planes[f];
             const float m = scan_dots<false>(L, nB, v3(pl.x, pl.y, pl.z));
             const float distance = fsub(m, pl.w);
             if (distance > best) { best = distance; bi = f; }
@@ -118,6 +120,13 @@ XD void face_query(const HullTable& T, const HullDesc& hA, const Fr& FinvA, cons
     out_d = best;
     out_face = bi;
     __syncwarp();
+}
+XD void face_query(const HullTable& T, const HullDesc& hA, const Fr& FinvA, const float* WB, int nB, float* L, int lane,
+                   float& out_d, int& out_face) {
+    const float4* planes = reinterpret_cast<const float4*>(T.words + hA.plane_off);
+    const int nF = hA.n_faces;
+    if (nF == 6 && nB == 8) face_query_t<6, 8>(planes, nF, FinvA, WB, nB, L, lane, out_d, out_face);
+    else face_query_t<0, 0>(planes, nF, FinvA, WB, nB, L, lane, out_d, out_face);
 }
 
 // Plane::from_point_normal (src/geometry.rs:27-36): displacement only.
@@ -136,39 +145,43 @@ XD float plane_displacement(V3 point, V3 normal) {
 //          distance; lane-local arg-max with the explicit "lower pair index wins ties" rule, which is what the
 //          serial scan's strict `>` amounts to (src/collision.rs:190).
 // Every value is computed by the same expression as before; only the schedule differs.
-XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const float* WA, const float* WB, V3 CA,
-                   float* Q, int lane, float& out_d, int& out_pair) {
+// NVA/NEA/NVB/NEB > 0: vertex / edge counts known at compile time (the cube-cube instantiation: the pair loop is
+// unrolled, index arithmetic and support scans are straight-line code); 0: taken from the run-time arguments.
+template <int NVA, int NEA, int NVB, int NEB>
+XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int nB_rt, int nEb_rt, const float* WA,
+                     const float* WB, V3 CA, float* Q, int lane, float& out_d, int& out_pair) {
     float best = -FLT_MAX;
     int bi = -1;
-    const int nEb = hB.n_edges, nPairs = hA.n_edges * nEb;
-    const int nA = hA.n_verts, nB = hB.n_verts;
+    const int nA = NVA ? NVA : nA_rt, nB = NVB ? NVB : nB_rt;
+    const int nEb = NEB ? NEB : nEb_rt, nPairs = (NEA ? NEA : nEa_rt) * nEb;
     float4* Q4v = reinterpret_cast<float4*>(Q);
     auto second_half = [&](float4 q) {
         const V3 axis = v3(q.x, q.y, q.z);
         const int e = __float_as_int(q.w);  // ia << 16 | jb: same order as the flat pair index
-        const V3 foot = ld3(WA, T.edge(hA, e >> 16).x);
+        const V3 foot = ld3(WA, EA[e >> 16].x);
         const float disp = plane_displacement(foot, axis);
         // plane.distance(B.support(-axis)) = min_v dot(axis, v) - displacement
-        const float sb = scan_dots<false>(WB, nB, axis);
+        const float sb = NVB ? scan_dots_t<NVB, false>(WB, nB, axis) : scan_dots<false>(WB, nB, axis);
         const float distance = fsub(sb, disp);
         if (distance > best || (distance == best && e < bi)) { best = distance; bi = e; }
     };
     int qn = 0;  // warp-uniform
     const int step_a = 32 / nEb, step_b = 32 - step_a * nEb;  // advancing the flat pair index by 32
     int ia = lane / nEb, jb = lane - ia * nEb;
+#pragma unroll
     for (int e0 = 0; e0 < nPairs; e0 += 32) {
         const int e = e0 + lane;
         bool pass = false;
         V3 axis = v3(0.f, 0.f, 0.f);
-        if (e < nPairs) {
-            const int2 ea = T.edge(hA, ia), eb = T.edge(hB, jb);
+        if (e0 + 32 <= nPairs || e < nPairs) {
+            const int2 ea = EA[ia], eb = EB[jb];
             const V3 foot = ld3(WA, ea.x);
             const V3 edge_a = ld3(WA, ea.y) - foot;
             const V3 edge_b = ld3(WB, eb.y) - ld3(WB, eb.x);
             axis = normalize(cross(edge_a, edge_b));  // parallel edges -> NaN axis, no guard (as the reference)
             if (dot(axis, foot - CA) < 0.0f) axis = -axis;
             // Ignore if another point on `a` is further in the direction to `b`.
-            const float sa = scan_dots<true>(WA, nA, axis);  // dot(v, axis) == dot(axis, v): IEEE multiplication commutes
+            const float sa = NVA ? scan_dots_t<NVA, true>(WA, nA, axis) : scan_dots<true>(WA, nA, axis);  // dot(v, axis) == dot(axis, v): IEEE multiplication commutes
             pass = !(sa > dot(foot, axis));
         }
         const unsigned m = __ballot_sync(0xffffffffu, pass);
@@ -188,6 +201,16 @@ XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, c
     warp_argmax_first(best, bi);
     out_d = best;
     out_pair = bi < 0 ? -1 : (bi >> 16) * nEb + (bi & 0xffff);  // flat pair index ia * nEdgesB + jb
+}
+XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const float* WA, const float* WB, V3 CA,
+                   float* Q, int lane, float& out_d, int& out_pair) {
+    const int2* EA = reinterpret_cast<const int2*>(T.words + hA.edge_off);
+    const int2* EB = reinterpret_cast<const int2*>(T.words + hB.edge_off);
+    const int nA = hA.n_verts, nEa = hA.n_edges, nB = hB.n_verts, nEb = hB.n_edges;
+    if (nA == 8 && nEa == 12 && nB == 8 && nEb == 12)
+        edge_query_t<8, 12, 8, 12>(EA, EB, nA, nEa, nB, nEb, WA, WB, CA, Q, lane, out_d, out_pair);
+    else
+        edge_query_t<0, 0, 0, 0>(EA, EB, nA, nEa, nB, nEb, WA, WB, CA, Q, lane, out_d, out_pair);
 }
 
 // Result of the three queries for one body pair, kept until the per-lane manifold pass.

@@ -201,7 +201,10 @@ __global__ void __launch_bounds__(256) stage_prepare_kernel(StagedParams P) {
 }
 
 // ---- stage 2: SAT queries (warp per candidate pair) -------------------------------------------------------
-__global__ void __launch_bounds__(256) stage_sat_kernel(StagedParams P) {
+#ifndef XPBD_SAT_MIN_BLOCKS
+#define XPBD_SAT_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_kernel(StagedParams P) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ __align__(8) uint64_t bar;
     stage_bulk(smem, P.hull_blob, P.hull_blob_bytes, &bar, reinterpret_cast<unsigned int*>(P.counters + 2));
@@ -387,7 +390,10 @@ __global__ void __launch_bounds__(128) stage_solve_kernel(StagedParams P) {
     const int side = (int)(t & 1), lane = threadIdx.x & 31;
     const unsigned pm = 3u << (lane & ~1);
     unsigned applied = 0;
-    if (blockIdx.x == 0 && threadIdx.x == 0) *P.S.work_count = 0;  // consumed by sat + manifold; next substep appends again
+    if (blockIdx.x == 0 && threadIdx.x == 0) {  // consumed by sat + manifold; the next substep appends again
+        P.counters[3] = *P.S.work_count;        // candidates of this substep (statistics)
+        *P.S.work_count = 0;
+    }
     if (world < P.n_worlds) {
         const StepConsts sc = P.sc;
         const int n_ground = P.S.n_ground[world], n_pairs = P.S.n_pairs[world];
@@ -579,13 +585,18 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
     const unsigned grid_solve = (unsigned)((2 * P.n_worlds + 127) / 128);
     const int total = substeps * n_frames;
     for (int s = 0; s < total; ++s) {
+        const bool timed = s == total - 1;  // per-stage device times of the last substep (xpbd_step_stats.stage_ms)
+        if (timed) cudaEventRecord(b->ev_stage[0], b->stream);
         stage_prepare_kernel<<<st->grid_prepare, 32 * st->warps_prepare, st->smem_prepare, b->stream>>>(P);
-        if (P.body_body) {
-            stage_sat_kernel<<<st->grid_sat, 256, st->smem_sat, b->stream>>>(P);
-            stage_manifold_kernel<<<st->grid_manifold, 128, st->smem_manifold, b->stream>>>(P);
-        }
+        if (timed) cudaEventRecord(b->ev_stage[1], b->stream);
+        if (P.body_body) stage_sat_kernel<<<st->grid_sat, 256, st->smem_sat, b->stream>>>(P);
+        if (timed) cudaEventRecord(b->ev_stage[2], b->stream);
+        if (P.body_body) stage_manifold_kernel<<<st->grid_manifold, 128, st->smem_manifold, b->stream>>>(P);
+        if (timed) cudaEventRecord(b->ev_stage[3], b->stream);
         stage_solve_kernel<<<grid_solve, 128, 0, b->stream>>>(P);
+        if (timed) cudaEventRecord(b->ev_stage[4], b->stream);
     }
+    b->stage_timed = true;
     XPBD_CUDA_TRY(cudaGetLastError());
     b->last.kernel_launches = total * (P.body_body ? 4 : 2);
     return XPBD_OK;

@@ -166,4 +166,6 @@ class Worlds:
     def stats(self) -> dict:
         s = _abi.StepStatsC()
         _abi.check(self._lib.xpbd_batch_last_stats(self._h, C.byref(s)))
-        return {f: getattr(s, f) for f, _ in s._fields_}
+        out = {f: getattr(s, f) for f, _ in s._fields_}
+        out["stage_ms"] = [float(x) for x in s.stage_ms]
+        return out

@@ -118,6 +118,10 @@ typedef struct xpbd_step_stats {
     uint64_t overflow_worlds;   /* worlds that hit the per-world contact capacity (0 in a valid run) */
     float elapsed_ms;           /* device time of the last step call (CUDA events on the batch stream) */
     int32_t kernel_launches;    /* kernels launched by the last step call */
+    /* Multi-body staged pipeline only (0 otherwise): device time of each stage's kernel in the LAST substep of the
+     * call (prepare, sat, manifold, solve) and the number of candidate body pairs that substep's SAT stage processed. */
+    float stage_ms[4];
+    uint64_t candidate_pairs;
 } xpbd_step_stats;
 
 /* ---- library / device ---------------------------------------------------------------- */

@@ -90,6 +90,8 @@ pub struct xpbd_step_stats {
     pub overflow_worlds: u64,
     pub elapsed_ms: f32,
     pub kernel_launches: i32,
+    pub stage_ms: [f32; 4],
+    pub candidate_pairs: u64,
 }
 
 #[repr(C)]
