@@ -356,6 +356,15 @@ def main():
             }
             if "fp32" in line["roofline"]["step"]:
                 line["roofline"]["fp32"] = line["roofline"]["step"].pop("fp32")
+        # roofline.traffic: DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/)
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                tr = json.load(f).get(args.workload)
+            if tr:
+                line["roofline"]["traffic"] = tr["dram_bytes_per_launch"] * (n_worlds / tr["worlds"])
+                line["roofline"]["traffic_source"] = tr["source"]
+        except Exception:
+            pass
         if not args.no_cpu_baseline and world_size == 1:
             try:
                 v, cores, sample, extra = cpu_baseline(args.workload, cfg)
