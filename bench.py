@@ -356,6 +356,15 @@ def main():
             }
             if "fp32" in line["roofline"]["step"]:
                 line["roofline"]["fp32"] = line["roofline"]["step"].pop("fp32")
+                if args.workload == "c3":
+                    # FP32 work of one cube-cube candidate = 17 650 thread-level FADD/FMUL/FFMA instructions (ncu
+                    # smsp__sass_thread_inst_executed_op_f{add,mul,ffma}_pred_on of stage_sat_kernel, profiles/r01d_stage_sat.txt):
+                    # the arithmetic of the reference's brute-force face + edge queries, nothing recomputed.
+                    fp = line["roofline"]["fp32"]
+                    fp["flops_per_pair"] = 17650.0
+                    fp["achieved"] = cand_pairs * 17650.0 / (stage_ms[1] * 1e-3) / 1e12
+                    fp["frac"] = fp["achieved"] / fp["peak"]
+                    fp["kernel"] = "stage_sat_kernel"
         # roofline.traffic: DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/)
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
