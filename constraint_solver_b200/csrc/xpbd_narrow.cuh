@@ -238,27 +238,71 @@ struct Manifold {
     V3 target[kMaxManifold];  // on the reference body (projection on the reference plane)
 };
 
-// Clip polygon `in` (n points) against the half-space dot(s, p - o) <= 0.
-XD int clip_polygon(const V3* in, int n, V3 o, V3 s, V3* out) {
+// Scratch of face_manifold: two polygon buffers and one depth array of kMaxClip entries each.
+// ClipLocal: thread-private arrays (local memory) — the fused kernel and the query kernels.
+struct ClipLocal {
+    V3 buf[2][kMaxClip];
+    float dep[kMaxClip];
+    XD V3 get(int w, int k) const { return buf[w][k]; }
+    XD void set(int w, int k, V3 v) { buf[w][k] = v; }
+    XD float depth(int k) const { return dep[k]; }
+    XD void set_depth(int k, float d) { dep[k] = d; }
+    XD bool overflowed() const { return false; }
+};
+// ClipShared: the same arrays in shared memory, word-interleaved across the block's threads (bank-conflict free),
+// with room for CAP <= kMaxClip entries.  A convex polygon gains at most one vertex per clip plane, so
+// CAP = 2 x the largest face never overflows geometrically; should rounding noise ever produce more, the entry is
+// dropped, overflowed() reports it and the caller repeats the pair with ClipLocal (kMaxClip, the specification's cap).
+template <int CAP, int STRIDE>  // entries per buffer, threads per block (compile-time: addresses fold into immediates)
+struct ClipShared {
+    float* base;  // already offset by the thread's index inside the block
+    bool over = false;
+    static constexpr int kWordsPerThread = 7 * CAP;
+    XD static constexpr int word(int w, int k, int c) { return ((w * CAP + k) * 3 + c) * STRIDE; }
+    XD V3 get(int w, int k) const {
+        k = k < CAP ? k : CAP - 1;  // only reachable after an overflow (result discarded): stay inside the scratch
+        const float* p = base + word(w, k, 0);
+        return v3(p[0], p[STRIDE], p[2 * STRIDE]);
+    }
+    XD void set(int w, int k, V3 v) {
+        if (k >= CAP) { over = true; return; }
+        float* p = base + word(w, k, 0);
+        p[0] = v.x; p[STRIDE] = v.y; p[2 * STRIDE] = v.z;
+    }
+    XD float depth(int k) const { return base[(6 * CAP + (k < CAP ? k : CAP - 1)) * STRIDE]; }
+    XD void set_depth(int k, float d) { if (k < CAP) base[(6 * CAP + k) * STRIDE] = d; }
+    XD bool overflowed() const { return over; }
+};
+
+// Clip polygon `src` (n points) against the half-space dot(s, p - o) <= 0 into polygon `dst`.
+template <class Clip>
+XD int clip_polygon(Clip& C, int src, int n, V3 o, V3 s, int dst) {
     int m = 0;
+    V3 p1 = C.get(src, 0);
+    float d1 = dot(s, p1 - o);
+    const V3 first = p1;
+    const float dfirst = d1;
     for (int k = 0; k < n; ++k) {
-        const V3 p1 = in[k], p2 = in[(k + 1 == n) ? 0 : k + 1];
-        const float d1 = dot(s, p1 - o), d2 = dot(s, p2 - o);
+        const bool last = k + 1 == n;
+        const V3 p2 = last ? first : C.get(src, k + 1);
+        const float d2 = last ? dfirst : dot(s, p2 - o);
         const bool in1 = d1 <= 0.0f, in2 = d2 <= 0.0f;
         if (in1 != in2) {
             const float t = fdiv(d1, fsub(d1, d2));
-            if (m < kMaxClip) out[m++] = p1 + (p2 - p1) * t;
+            if (m < kMaxClip) C.set(dst, m++, p1 + (p2 - p1) * t);
         }
         if (in2) {
-            if (m < kMaxClip) out[m++] = p2;
+            if (m < kMaxClip) C.set(dst, m++, p2);
         }
+        p1 = p2; d1 = d2;
     }
     return m;
 }
 
 // Face contact: reference body R (face r, frame FR, world verts WR), incident body I.  One lane.
+template <class Clip>
 XD void face_manifold(const HullTable& T, const HullDesc& hR, const HullDesc& hI, const Fr& FR, const Fr& FI,
-                      const float* WR, const float* WI, int r, Manifold& out) {
+                      const float* WR, const float* WI, int r, Clip& C, Manifold& out) {
     out.count = 0;
     // ref_plane = frames.0 * polytopes.0.plane(face)  (src/collision.rs:66, src/frame.rs:55-64)
     const float4 pl = T.plane(hR, r);
@@ -275,13 +319,11 @@ XD void face_manifold(const HullTable& T, const HullDesc& hR, const HullDesc& hI
         if (d < least) { least = d; inc = k; }
     }
     if (inc < 0) return;
-    V3 bufA[kMaxClip], bufB[kMaxClip];
     int cnt = 0;
     for (int k = T.face_begin(hI, inc); k < T.face_begin(hI, inc + 1); ++k)
-        if (cnt < kMaxClip) bufA[cnt++] = ld3(WI, T.face_vertex(hI, k));
+        if (cnt < kMaxClip) C.set(0, cnt++, ld3(WI, T.face_vertex(hI, k)));
     const int rb = T.face_begin(hR, r), nr = T.face_begin(hR, r + 1) - rb;
-    V3* src = bufA;
-    V3* dst = bufB;
+    int src = 0;
     for (int m = 0; m < nr && cnt > 0; ++m) {
         const int m1 = (m + 1 >= nr) ? m + 1 - nr : m + 1, m2 = (m + 2 >= nr) ? m + 2 - nr : m + 2;
         const V3 w0 = ld3(WR, T.face_vertex(hR, rb + m));
@@ -289,51 +331,60 @@ XD void face_manifold(const HullTable& T, const HullDesc& hR, const HullDesc& hI
         const V3 w2 = ld3(WR, T.face_vertex(hR, rb + m2));
         V3 s = cross(w1 - w0, n);
         if (dot(s, w2 - w0) > 0.0f) s = -s;
-        cnt = clip_polygon(src, cnt, w0, s, dst);
-        V3* t = src; src = dst; dst = t;
+        cnt = clip_polygon(C, src, cnt, w0, s, src ^ 1);
+        src ^= 1;
     }
-    // keep points strictly below the reference plane (compacted in place into dst)
-    float depth[kMaxClip];
+    // keep points strictly below the reference plane (compacted into the other buffer)
+    const int dst = src ^ 1;
     int c = 0;
     for (int k = 0; k < cnt; ++k) {
-        const float d = fsub(dot(n, src[k]), disp);
-        if (d < 0.0f) { dst[c] = src[k]; depth[c] = d; ++c; }
+        const V3 p = C.get(src, k);
+        const float d = fsub(dot(n, p), disp);
+        if (d < 0.0f) { C.set(dst, c, p); C.set_depth(c, d); ++c; }
     }
-    int keep[kMaxManifold];
-    int nk = 0;
-    if (c <= kMaxManifold) {
-        for (int k = 0; k < c; ++k) keep[nk++] = k;
-    } else {
+    if (C.overflowed()) return;
+    // the (up to four) kept points, in polygon order; scalars + compare-exchange network instead of an indexed array
+    // (same result as an insertion sort: the four indices are distinct)
+    int k0 = 0, k1 = 1, k2 = 2, k3 = 3, nk = c;
+    if (c > kMaxManifold) {
         int i0 = 0;
-        for (int k = 1; k < c; ++k) if (depth[k] < depth[i0]) i0 = k;
+        float dmin = C.depth(0);
+        for (int k = 1; k < c; ++k) { const float d = C.depth(k); if (d < dmin) { dmin = d; i0 = k; } }
+        const V3 q0 = C.get(dst, i0);
         int i1 = -1;
         float far = -1.0f;
         for (int k = 0; k < c; ++k) {
             if (k == i0) continue;
-            const float d2 = magnitude2(dst[k] - dst[i0]);
+            const float d2 = magnitude2(C.get(dst, k) - q0);
             if (d2 > far) { far = d2; i1 = k; }
         }
         int i2 = -1, i3 = -1;
         float amax = 0.0f, amin = 0.0f;
-        const V3 e01 = dst[i1] - dst[i0];
+        const V3 e01 = C.get(dst, i1) - q0;
         for (int k = 0; k < c; ++k) {
             if (k == i0 || k == i1) continue;
-            const float area = dot(cross(e01, dst[k] - dst[i0]), n);
+            const float area = dot(cross(e01, C.get(dst, k) - q0), n);
             if (area > amax) { amax = area; i2 = k; }
             if (area < amin) { amin = area; i3 = k; }
         }
-        keep[nk++] = i0; keep[nk++] = i1;
-        if (i2 >= 0) keep[nk++] = i2;
-        if (i3 >= 0) keep[nk++] = i3;
-        for (int a = 1; a < nk; ++a)  // insertion sort: polygon order
-            for (int b = a; b > 0 && keep[b] < keep[b - 1]; --b) { int t = keep[b]; keep[b] = keep[b - 1]; keep[b - 1] = t; }
+        constexpr int kAbsent = 1 << 20;  // sorts behind every real index
+        k0 = i0; k1 = i1; k2 = i2 >= 0 ? i2 : kAbsent; k3 = i3 >= 0 ? i3 : kAbsent;
+        nk = 2 + (i2 >= 0) + (i3 >= 0);
+        int t;
+#define XPBD_CSWAP(a, b) if (b < a) { t = a; a = b; b = t; }
+        XPBD_CSWAP(k0, k1) XPBD_CSWAP(k2, k3) XPBD_CSWAP(k0, k2) XPBD_CSWAP(k1, k3) XPBD_CSWAP(k1, k2)
+#undef XPBD_CSWAP
     }
-    for (int k = 0; k < nk; ++k) {
-        const V3 p = dst[keep[k]];
-        out.point[out.count] = p;
-        out.target[out.count] = p - depth[keep[k]] * n;  // Plane::project
-        ++out.count;
+    const int kept[kMaxManifold] = {k0, k1, k2, k3};
+#pragma unroll
+    for (int k = 0; k < kMaxManifold; ++k) {
+        if (k < nk) {
+            const V3 p = C.get(dst, kept[k]);
+            out.point[k] = p;
+            out.target[k] = p - C.depth(kept[k]) * n;  // Plane::project
+        }
     }
+    out.count = nk;
 }
 
 XD float clamp01(float x) { return x < 0.0f ? 0.0f : (x > 1.0f ? 1.0f : x); }
@@ -354,8 +405,9 @@ XD void edge_manifold(V3 p1, V3 q1, V3 p2, V3 q2, Manifold& out) {
 }
 
 // Manifold of one pair from its chosen feature. `incident` = 0: contact points ride on A, 1: on B.
+template <class Clip>
 XD void pair_manifold(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const Fr& FA, const Fr& FB,
-                      const float* WA, const float* WB, PairFeature pf, Manifold& m, int& incident) {
+                      const float* WA, const float* WB, PairFeature pf, Clip& C, Manifold& m, int& incident) {
     m.count = 0;
     incident = 0;
     if (pf.feature == kEdgeEdge) {
@@ -364,12 +416,17 @@ XD void pair_manifold(const HullTable& T, const HullDesc& hA, const HullDesc& hB
         edge_manifold(ld3(WA, ea.x), ld3(WA, ea.y), ld3(WB, eb.x), ld3(WB, eb.y), m);
         incident = 0;
     } else if (pf.feature == kFaceB) {
-        face_manifold(T, hB, hA, FB, FA, WB, WA, pf.index, m);  // B is the reference, A's face is clipped
+        face_manifold(T, hB, hA, FB, FA, WB, WA, pf.index, C, m);  // B is the reference, A's face is clipped
         incident = 0;
     } else if (pf.feature == kFaceA) {
-        face_manifold(T, hA, hB, FA, FB, WA, WB, pf.index, m);
+        face_manifold(T, hA, hB, FA, FB, WA, WB, pf.index, C, m);
         incident = 1;
     }
+}
+XD void pair_manifold(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const Fr& FA, const Fr& FB,
+                      const float* WA, const float* WB, PairFeature pf, Manifold& m, int& incident) {
+    ClipLocal C;
+    pair_manifold(T, hA, hB, FA, FB, WA, WB, pf, C, m, incident);
 }
 
 }  // namespace xpbd

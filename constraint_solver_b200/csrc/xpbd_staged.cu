@@ -28,7 +28,6 @@
 namespace xpbd {
 
 constexpr int kGroundWords = 8;    // head, contact0.xyz, direction.xyz, distance
-constexpr int kContactWords = 12;  // head, a.xyz | b.xyz, - | normal.xyz, -   (three float4)
 
 struct StagedBuffers {
     float4* ppos = nullptr;   // per body: pose at the start of the substep
@@ -68,6 +67,7 @@ struct StagedParams {
     StepConsts sc;
     float friction;
     int body_body;
+    int pair_table_len;  // B(B-1)/2 when stage_prepare keeps the pair table in shared memory, else 0
     unsigned long long* counters;  // [0] constraints, [1] overflow worlds, [2] tma fallbacks
 };
 
@@ -75,24 +75,50 @@ struct StagedParams {
 // per-warp shared scratch, words per body: fpos 3, pfpos 3, finvp 3, cen 3, rot 4, prot 4, hull 1
 constexpr int kPrepWordsPerBody = 21;
 
-__global__ void __launch_bounds__(256) stage_prepare_kernel(StagedParams P) {
+#ifndef XPBD_PREP_MIN_BLOCKS
+#define XPBD_PREP_MIN_BLOCKS 4
+#endif
+// G = lanes per world: worlds of up to 16 bodies share a warp two at a time (half-warp each; ballots are masked and
+// shifted to the half), larger worlds take the whole warp.  Per block, after the hull table and the per-world
+// scratch, shared memory holds the table of body pairs (i | j << 16, i < j, lexicographic) when it fits
+// (P.pair_table_len > 0): the broadphase then runs over the flattened pair index — ceil(B(B-1)/2 / G) ballot
+// rounds per world instead of (B-1) x ceil(B / G).
+template <int G>
+__global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kernel(StagedParams P) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ __align__(8) uint64_t bar;
     stage_bulk(smem, P.hull_blob, P.hull_blob_bytes, &bar, reinterpret_cast<unsigned int*>(P.counters + 2));
     const HullTable T{smem};
+    constexpr int NG = 32 / G;
+    constexpr unsigned kFull = 0xffffffffu;
     const int B = P.B, maxV = P.S.maxV;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    float* W = reinterpret_cast<float*>(smem) + P.hull_blob_bytes / 4 + (size_t)warp * kPrepWordsPerBody * B;
+    const int grp = lane / G, gl = lane % G;
+    const int gshift = grp * G;
+    const unsigned gmask = G == 32 ? kFull : (((1u << (G & 31)) - 1u) << gshift);
+    const unsigned below_me = (1u << gl) - 1u;
+    float* W = reinterpret_cast<float*>(smem) + P.hull_blob_bytes / 4 + (size_t)(warp * NG + grp) * kPrepWordsPerBody * B;
     float* s_fpos = W; float* s_pfpos = W + 3 * B; float* s_finvp = W + 6 * B; float* s_cen = W + 9 * B;
     float* s_rot = W + 12 * B; float* s_prot = W + 16 * B;
     int* s_hull = reinterpret_cast<int*>(W + 20 * B);
+    uint32_t* pair_table = smem + P.hull_blob_bytes / 4 + (size_t)nwarps * NG * kPrepWordsPerBody * B;
+    const int n_table = P.pair_table_len;
+    if (n_table > 0) {
+        for (int i = threadIdx.x; i + 1 < B; i += blockDim.x) {
+            const int row = (i * (2 * B - i - 1)) / 2;  // pairs before row i
+            for (int j = i + 1; j < B; ++j) pair_table[row + j - i - 1] = (uint32_t)i | ((uint32_t)j << 16);
+        }
+        __syncthreads();
+    }
     const StepConsts sc = P.sc;
 
-    for (int64_t world = (int64_t)blockIdx.x * nwarps + warp; world < P.n_worlds; world += (int64_t)gridDim.x * nwarps) {
+    for (int64_t w0 = ((int64_t)blockIdx.x * nwarps + warp) * NG; w0 < P.n_worlds; w0 += (int64_t)gridDim.x * nwarps * NG) {
+        const int64_t world = w0 + grp;
+        const bool valid = world < P.n_worlds;  // odd world count: the second half of the last warp idles
         const int64_t g0 = world * B;
         bool overflow = false;
         // --- bodies: save past, Rigid::integrate, frames (lanes over bodies)
-        for (int b = lane; b < B; b += 32) {
+        for (int b = gl; b < B && valid; b += G) {
             const int64_t g = g0 + b;
             BodyDyn d; BodyConst k;
             load_dyn(P.bodies, g, d);
@@ -118,13 +144,13 @@ __global__ void __launch_bounds__(256) stage_prepare_kernel(StagedParams P) {
         int n_ground = 0;
         {
             float* gc = P.S.gcons + (size_t)world * P.S.capG * kGroundWords;
-            int b = 0, v = lane;
-            for (int t0 = 0; t0 < B * maxV; t0 += 32) {
+            int b = 0, v = gl;
+            for (int t0 = 0; t0 < B * maxV; t0 += G) {
                 while (v >= maxV) { v -= maxV; ++b; }
                 bool below = false;
                 V3 p = v3(0.f, 0.f, 0.f);
                 Fr frame;
-                if (b < B) {
+                if (valid && b < B) {
                     const HullDesc& hd = T.desc(s_hull[b]);
                     if (v < hd.n_verts) {
                         frame.p = sld3(s_fpos, B, b); frame.q = sldq(s_rot, B, b);
@@ -133,9 +159,9 @@ __global__ void __launch_bounds__(256) stage_prepare_kernel(StagedParams P) {
                         below = !(p.z >= 0.0f);
                     }
                 }
-                const unsigned m = __ballot_sync(0xffffffffu, below);
+                const unsigned m = (__ballot_sync(kFull, below) & gmask) >> gshift;
                 if (below) {
-                    const int idx = n_ground + __popc(m & ((1u << lane) - 1u));
+                    const int idx = n_ground + __popc(m & below_me);
                     if (idx < P.S.capG) {
                         Fr past, finv;
                         past.p = sld3(s_pfpos, B, b); past.q = sldq(s_prot, B, b);
@@ -156,46 +182,68 @@ __global__ void __launch_bounds__(256) stage_prepare_kernel(StagedParams P) {
                     }
                 }
                 n_ground += __popc(m);
-                v += 32;
+                v += G;
             }
         }
         // --- broadphase: bounding spheres about the hull centroids, pairs i<j in lexicographic order
         int n_pairs = 0;
         if (P.body_body) {
             int4* pairs = P.S.pairs + (size_t)world * P.S.capP;
-            for (int i = 0; i + 1 < B; ++i) {
-                const V3 ci = sld3(s_cen, B, i);
-                const float ri = T.desc(s_hull[i]).radius;
-                for (int j0 = i + 1; j0 < B; j0 += 32) {
-                    const int j = j0 + lane;
+            if (n_table > 0) {
+                for (int p0 = 0; p0 < n_table; p0 += G) {
+                    const int p = p0 + gl;
                     bool cand = false;
-                    if (j < B) {
-                        const V3 d = sld3(s_cen, B, j) - ci;
-                        const float rsum = fadd(ri, T.desc(s_hull[j]).radius);
+                    uint32_t ij = 0;
+                    if (valid && p < n_table) {
+                        ij = pair_table[p];
+                        const int i = ij & 0xffff, j = ij >> 16;
+                        const V3 d = sld3(s_cen, B, j) - sld3(s_cen, B, i);
+                        const float rsum = fadd(T.desc(s_hull[i]).radius, T.desc(s_hull[j]).radius);
                         cand = !(magnitude2(d) > fmul(rsum, rsum));
                     }
-                    const unsigned m = __ballot_sync(0xffffffffu, cand);
+                    const unsigned m = (__ballot_sync(kFull, cand) & gmask) >> gshift;
                     if (cand) {
-                        const int idx = n_pairs + __popc(m & ((1u << lane) - 1u));
-                        if (idx < P.S.capP) pairs[idx] = make_int4(i | (j << 16), kNone, -1, 0);
+                        const int idx = n_pairs + __popc(m & below_me);
+                        if (idx < P.S.capP) pairs[idx] = make_int4((int)ij, kNone, -1, 0);
                         else overflow = true;
                     }
                     n_pairs += __popc(m);
+                }
+            } else {
+                for (int i = 0; i + 1 < B; ++i) {
+                    const V3 ci = sld3(s_cen, B, i);
+                    const float ri = T.desc(s_hull[i]).radius;
+                    for (int j0 = i + 1; j0 < B; j0 += G) {
+                        const int j = j0 + gl;
+                        bool cand = false;
+                        if (valid && j < B) {
+                            const V3 d = sld3(s_cen, B, j) - ci;
+                            const float rsum = fadd(ri, T.desc(s_hull[j]).radius);
+                            cand = !(magnitude2(d) > fmul(rsum, rsum));
+                        }
+                        const unsigned m = (__ballot_sync(kFull, cand) & gmask) >> gshift;
+                        if (cand) {
+                            const int idx = n_pairs + __popc(m & below_me);
+                            if (idx < P.S.capP) pairs[idx] = make_int4(i | (j << 16), kNone, -1, 0);
+                            else overflow = true;
+                        }
+                        n_pairs += __popc(m);
+                    }
                 }
             }
             if (n_pairs > P.S.capP) n_pairs = P.S.capP;
             // append this world's candidates to the global work list (order irrelevant: results land in the slots)
             unsigned base = 0;
-            if (lane == 0 && n_pairs) base = atomicAdd(P.S.work_count, (unsigned)n_pairs);
-            base = __shfl_sync(0xffffffffu, base, 0);
+            if (gl == 0 && n_pairs) base = atomicAdd(P.S.work_count, (unsigned)n_pairs);
+            base = __shfl_sync(kFull, base, gshift);
             __syncwarp();  // the pair slots written above are read back by other lanes
-            for (int p = lane; p < n_pairs; p += 32) {
+            for (int p = gl; p < n_pairs; p += G) {
                 const int ij = pairs[p].x;
                 P.S.worklist[base + p] = make_int4((int)(world * P.S.capP + p), ij, s_hull[ij & 0xffff] | (s_hull[ij >> 16] << 16), 0);
             }
         }
-        overflow = __any_sync(0xffffffffu, overflow);
-        if (lane == 0) {
+        overflow = (__ballot_sync(kFull, overflow) & gmask) != 0;
+        if (gl == 0 && valid) {
             P.S.n_ground[world] = n_ground < P.S.capG ? n_ground : P.S.capG;
             P.S.n_pairs[world] = n_pairs;
             if (overflow && atomicExch(&P.S.overflow[world], 1) == 0) atomicAdd(P.counters + 1, 1ull);
@@ -255,13 +303,21 @@ __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_kernel(Sta
 }
 
 // ---- stage 3: manifolds (thread per candidate pair) -> fresh contacts in the pair's slot --------------------
-__global__ void __launch_bounds__(128) stage_manifold_kernel(StagedParams P) {
+#ifndef XPBD_MANIFOLD_MIN_BLOCKS
+#define XPBD_MANIFOLD_MIN_BLOCKS 4
+#endif
+constexpr int kManifoldThreads = 128;
+template <int CAP>
+__global__ void __launch_bounds__(kManifoldThreads, XPBD_MANIFOLD_MIN_BLOCKS) stage_manifold_kernel(StagedParams P) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ __align__(8) uint64_t bar;
     stage_bulk(smem, P.hull_blob, P.hull_blob_bytes, &bar, reinterpret_cast<unsigned int*>(P.counters + 2));
     const HullTable T{smem};
     const int B = P.B, maxV = P.S.maxV;
     const unsigned count = *P.S.work_count;
+    // clip polygons live in shared memory (thread-private arrays would be local memory: ~0.5 KB per candidate of
+    // L2/HBM round trips, measured as 3x the stage's algorithmic traffic)
+    ClipShared<CAP, kManifoldThreads> clip{reinterpret_cast<float*>(smem) + P.hull_blob_bytes / 4 + threadIdx.x};
     for (unsigned it = blockIdx.x * blockDim.x + threadIdx.x; it < count; it += gridDim.x * blockDim.x) {
         const uint32_t slot = (uint32_t)P.S.worklist[it].x;
         const int4 pr = P.S.pairs[slot];
@@ -278,9 +334,13 @@ __global__ void __launch_bounds__(128) stage_manifold_kernel(StagedParams P) {
             FB.p = v3(pb.x, pb.y, pb.z); FB.q = q4(rb.w, rb.x, rb.y, rb.z);
             Manifold m;
             int incident;
-            pair_manifold(T, T.desc(P.hull_ids ? P.hull_ids[gi] : 0), T.desc(P.hull_ids ? P.hull_ids[gj] : 0), FA, FB,
-                          reinterpret_cast<const float*>(P.S.verts + gi * maxV),
-                          reinterpret_cast<const float*>(P.S.verts + gj * maxV), pf, m, incident);
+            const HullDesc& hA = T.desc(P.hull_ids ? P.hull_ids[gi] : 0);
+            const HullDesc& hB = T.desc(P.hull_ids ? P.hull_ids[gj] : 0);
+            const float* WA = reinterpret_cast<const float*>(P.S.verts + gi * maxV);
+            const float* WB = reinterpret_cast<const float*>(P.S.verts + gj * maxV);
+            clip.over = false;
+            pair_manifold(T, hA, hB, FA, FB, WA, WB, pf, clip, m, incident);
+            if (clip.over) pair_manifold(T, hA, hB, FA, FB, WA, WB, pf, m, incident);  // never seen; exact by construction
             const int inc = incident == 0 ? i : j, oth = incident == 0 ? j : i;
             const int64_t ginc = world * B + inc, goth = world * B + oth;
             const float4 qi = P.bodies.dynC[ginc], qo = P.bodies.dynC[goth];
@@ -289,7 +349,9 @@ __global__ void __launch_bounds__(128) stage_manifold_kernel(StagedParams P) {
             finvI.q = conjugate(q4(qi.w, qi.x, qi.y, qi.z)); finvI.p = v3(fi.x, fi.y, fi.z);
             finvO.q = conjugate(q4(qo.w, qo.x, qo.y, qo.z)); finvO.p = v3(fo.x, fo.y, fo.z);
             float4* out = P.S.pcons + (size_t)slot * kMaxManifold * 3;
-            for (int k = 0; k < m.count; ++k) {
+#pragma unroll
+            for (int k = 0; k < kMaxManifold; ++k) {
+                if (k >= m.count) continue;
                 const V3 correction = m.target[k] - m.point[k];
                 if (magnitude2(correction) == 0.0f) continue;  // no direction: dropped
                 const V3 a = finvI * m.point[k];
@@ -390,18 +452,32 @@ struct CachedBody {
     XD void set_vel(int, V3 v, V3 w) { a4.w = v.x; b4 = make_float4(v.y, v.z, w.x, w.y); d1 = w.z; dirty = true; }
 };
 
-__global__ void __launch_bounds__(128) stage_solve_kernel(StagedParams P) {
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t world = t >> 1;
-    const int side = (int)(t & 1), lane = threadIdx.x & 31;
+// Which body of a contact this lane holds: 0 = the head's body a, 1 = body b.  When the two indices differ in
+// parity the lane keeps the body whose parity equals its side, so that in a chain of contacts (0,1), (1,2), (2,3) ...
+// — a stack — every body stays cached in ONE lane across consecutive manifolds instead of being written back by one
+// lane and re-read by the other.  The arithmetic per body does not depend on which lane performs it.
+XD int contact_role(int side, int head) {
+    const int a = head_a(head), b = head_b(head);
+    return ((a ^ b) & 1) ? (side ^ (a & 1)) : side;
+}
+
+#ifndef XPBD_SOLVE_MIN_BLOCKS
+#define XPBD_SOLVE_MIN_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel(StagedParams P) {
+    const int lane = threadIdx.x & 31;
+    const int side = lane & 1;
     const unsigned pm = 3u << (lane & ~1);
     unsigned applied = 0;
     if (blockIdx.x == 0 && threadIdx.x == 0) {  // consumed by sat + manifold; the next substep appends again
         P.counters[3] = *P.S.work_count;        // candidates of this substep (statistics)
         *P.S.work_count = 0;
     }
-    if (world < P.n_worlds) {
-        const StepConsts sc = P.sc;
+    const StepConsts sc = P.sc;
+    // grid-stride over worlds: the host may launch fewer blocks than worlds / 64 so that the worlds in flight
+    // (x ~2.6 KB each) stay inside the L2 instead of cycling through HBM between the sweep, derive and velocity phases
+    for (int64_t world = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 1; world < P.n_worlds;
+         world += ((int64_t)gridDim.x * blockDim.x) >> 1) {
         const int n_ground = P.S.n_ground[world], n_pairs = P.S.n_pairs[world];
         int4* pairs = P.S.pairs + (size_t)world * P.S.capP;
         float4* pc = P.S.pcons + (size_t)world * P.S.capP * kMaxManifold * 3;
@@ -411,9 +487,11 @@ __global__ void __launch_bounds__(128) stage_solve_kernel(StagedParams P) {
             const float4* gc = reinterpret_cast<const float4*>(P.S.gcons + (size_t)world * P.S.capG * kGroundWords);
             for (int k = 0; k < n_ground; ++k) {
                 const float4 c0 = gc[2 * k], c1 = gc[2 * k + 1];
-                const int me = side ? -1 : head_a(__float_as_int(c0.x));
+                const int a = head_a(__float_as_int(c0.x));
+                const int owner = a & 1;  // same lane that holds this body in a neighbouring contact
+                const int me = side == owner ? a : -1;
                 C.release(me); __syncwarp(pm); C.acquire(me);
-                if (side == 0) solve_ground(C, me, v3(c0.y, c0.z, c0.w), v3(c1.x, c1.y, c1.z), c1.w, sc);
+                if (side == owner) solve_ground(C, me, v3(c0.y, c0.z, c0.w), v3(c1.x, c1.y, c1.z), c1.w, sc);
             }
             applied += n_ground;
             // --- ... then the manifolds of the candidate pairs i<j in lexicographic order ...
@@ -423,11 +501,12 @@ __global__ void __launch_bounds__(128) stage_solve_kernel(StagedParams P) {
                     float4* c = pc + ((size_t)p * kMaxManifold + k) * 3;
                     const float4 c0 = c[0], c1 = c[1], c2 = c[2];
                     const int head = __float_as_int(c0.x);
-                    const int me = side ? head_b(head) : head_a(head);
+                    const int role = contact_role(side, head);
+                    const int me = role ? head_b(head) : head_a(head);
                     C.release(me); __syncwarp(pm); C.acquire(me);
-                    const bool active = solve_contact(C, side, pm, me, side ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w),
+                    const bool active = solve_contact(C, role, pm, me, role ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w),
                                                       v3(c2.x, c2.y, c2.z), sc);
-                    if (active && side == 0) c[0].x = __int_as_float(head | kActiveBit);
+                    if (active && role == 0) c[0].x = __int_as_float(head | kActiveBit);
                 }
                 applied += cnt;
             }
@@ -459,17 +538,20 @@ __global__ void __launch_bounds__(128) stage_solve_kernel(StagedParams P) {
                     const int head = __float_as_int(c0.x);
                     if (!(head & kActiveBit)) continue;
                     const float4 c1 = c[1], c2 = c[2];
-                    const int me = side ? head_b(head) : head_a(head);
+                    const int role = contact_role(side, head & ~kActiveBit);
+                    const int me = role ? head_b(head) : head_a(head);
                     C.release(me); __syncwarp(pm); C.acquire(me);
-                    velocity_contact(C, side, pm, me, side ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w), v3(c2.x, c2.y, c2.z),
+                    velocity_contact(C, role, pm, me, role ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w), v3(c2.x, c2.y, c2.z),
                                      P.friction);
                 }
             }
             C.flush();
         }
-        if (side) applied = 0;
+        __syncwarp(pm);
     }
-    // one atomic per warp
+    if (side) applied = 0;
+    // one atomic per warp (lanes leave the loop at different times: reconverge first)
+    __syncwarp();
     for (int o = 16; o > 0; o >>= 1) applied += __shfl_down_sync(0xffffffffu, applied, o);
     if (lane == 0 && applied) atomicAdd(P.counters, (unsigned long long)applied);
 }
@@ -482,6 +564,12 @@ struct StagedState {
     int grid_prepare = 0, grid_sat = 0, grid_manifold = 0;
     size_t smem_prepare = 0, smem_sat = 0, smem_manifold = 0;
     int warps_prepare = 8;
+    int clip_cap = kMaxClip;
+    void (*manifold_fn)(StagedParams) = nullptr;
+    void (*prepare_fn)(StagedParams) = nullptr;
+    int prepare_lanes = 32, pair_table_len = 0;
+    int n_sm = 148;
+    int solve_blocks_per_sm = 0;  // grid-stride over worlds: resident blocks per SM (occupancy), XPBD_SOLVE_BLOCKS_PER_SM overrides
 };
 
 void release_world_scratch(xpbd_batch* b) {
@@ -534,25 +622,40 @@ static int ensure_staged(xpbd_batch* b, StagedState*& out) {
     XPBD_CUDA_TRY(cudaGetDevice(&dev));
     XPBD_CUDA_TRY(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
     XPBD_CUDA_TRY(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    st->n_sm = n_sm;
+    {
+        int occ_solve = 1;
+        XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_solve, stage_solve_kernel, 128, 0));
+        st->solve_blocks_per_sm = occ_solve < 6 ? occ_solve : 6;  // measured on C3: 6 resident blocks beat 7, 8 and an unbounded grid (L2 working set)
+        if (const char* e = std::getenv("XPBD_SOLVE_BLOCKS_PER_SM")) st->solve_blocks_per_sm = std::atoi(e);
+    }
     // prepare: warps per block limited by the per-warp body scratch
-    const size_t prep_per_warp = (size_t)kPrepWordsPerBody * B * 4;
+    st->prepare_lanes = B <= 16 ? 16 : 32;  // lanes per world
+    st->prepare_fn = B <= 16 ? stage_prepare_kernel<16> : stage_prepare_kernel<32>;
+    const size_t prep_per_warp = (size_t)(32 / st->prepare_lanes) * kPrepWordsPerBody * B * 4;
+    const size_t n_pairs_all = (size_t)B * (B - 1) / 2;
+    st->pair_table_len = n_pairs_all <= 4096 ? (int)n_pairs_all : 0;  // <= 16 KB of shared memory
+    const size_t table_bytes = (size_t)st->pair_table_len * 4;
     int wp = 8;
-    while (wp > 1 && H.bytes + wp * prep_per_warp > (size_t)smem_max / 2) wp >>= 1;
+    while (wp > 1 && H.bytes + wp * prep_per_warp + table_bytes > (size_t)smem_max / 2) wp >>= 1;
     st->warps_prepare = wp;
-    st->smem_prepare = H.bytes + wp * prep_per_warp;
+    st->smem_prepare = H.bytes + wp * prep_per_warp + table_bytes;
     st->smem_sat = H.bytes + 8 * (size_t)(3 * kVertWords * S.maxV + kEdgeQueueWords) * 4;
-    st->smem_manifold = H.bytes;
-    if (st->smem_prepare > (size_t)smem_max || st->smem_sat > (size_t)smem_max)
+    st->clip_cap = 2 * H.max_face_verts <= 8 ? 8 : kMaxClip;  // entries per clip buffer in stage_manifold's scratch
+    st->smem_manifold = H.bytes + (size_t)kManifoldThreads * 7 * st->clip_cap * 4;
+    if (st->smem_prepare > (size_t)smem_max || st->smem_sat > (size_t)smem_max || st->smem_manifold > (size_t)smem_max)
         return fail(XPBD_ERR_CAPACITY, "hull table / world too large for shared memory (%zu, %zu bytes)", st->smem_prepare, st->smem_sat);
-    XPBD_CUDA_TRY(cudaFuncSetAttribute(stage_prepare_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_prepare));
+    XPBD_CUDA_TRY(cudaFuncSetAttribute(st->prepare_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_prepare));
     XPBD_CUDA_TRY(cudaFuncSetAttribute(stage_sat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_sat));
-    XPBD_CUDA_TRY(cudaFuncSetAttribute(stage_manifold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_manifold));
+    st->manifold_fn = st->clip_cap == 8 ? stage_manifold_kernel<8> : stage_manifold_kernel<kMaxClip>;
+    XPBD_CUDA_TRY(cudaFuncSetAttribute(st->manifold_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_manifold));
     int occ = 1;
-    XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, stage_prepare_kernel, 32 * wp, st->smem_prepare));
-    st->grid_prepare = (int)std::min<int64_t>((b->desc.n_worlds + wp - 1) / wp, (int64_t)n_sm * (occ > 0 ? occ : 1));
+    XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, st->prepare_fn, 32 * wp, st->smem_prepare));
+    const int64_t worlds_per_block = (int64_t)wp * (32 / st->prepare_lanes);
+    st->grid_prepare = (int)std::min<int64_t>((b->desc.n_worlds + worlds_per_block - 1) / worlds_per_block, (int64_t)n_sm * (occ > 0 ? occ : 1));
     XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, stage_sat_kernel, 256, st->smem_sat));
     st->grid_sat = (int)std::min<int64_t>(((int64_t)nw * S.capP + 7) / 8, (int64_t)n_sm * (occ > 0 ? occ : 1));
-    XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, stage_manifold_kernel, 128, st->smem_manifold));
+    XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, st->manifold_fn, kManifoldThreads, st->smem_manifold));
     st->grid_manifold = (int)std::min<int64_t>(((int64_t)nw * S.capP + 127) / 128, (int64_t)n_sm * (occ > 0 ? occ : 1));
     out = st;
     return XPBD_OK;
@@ -586,18 +689,20 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
     P.sc.compliance = (float)b->desc.compliance / (P.sc.dt * P.sc.dt);
     P.friction = (float)b->desc.friction;
     P.body_body = b->desc.body_body_contacts;
+    P.pair_table_len = st->pair_table_len;
     P.counters = b->d_counters;
     XPBD_CUDA_TRY(cudaMemsetAsync(st->buf.overflow, 0, (size_t)P.n_worlds * sizeof(int), b->stream));
-    const unsigned grid_solve = (unsigned)((2 * P.n_worlds + 127) / 128);
+    unsigned grid_solve = (unsigned)((2 * P.n_worlds + 127) / 128);
+    if (st->solve_blocks_per_sm > 0) grid_solve = std::min(grid_solve, (unsigned)(st->solve_blocks_per_sm * st->n_sm));
     const int total = substeps * n_frames;
     for (int s = 0; s < total; ++s) {
         const bool timed = s == total - 1;  // per-stage device times of the last substep (xpbd_step_stats.stage_ms)
         if (timed) cudaEventRecord(b->ev_stage[0], b->stream);
-        stage_prepare_kernel<<<st->grid_prepare, 32 * st->warps_prepare, st->smem_prepare, b->stream>>>(P);
+        st->prepare_fn<<<st->grid_prepare, 32 * st->warps_prepare, st->smem_prepare, b->stream>>>(P);
         if (timed) cudaEventRecord(b->ev_stage[1], b->stream);
         if (P.body_body) stage_sat_kernel<<<st->grid_sat, 256, st->smem_sat, b->stream>>>(P);
         if (timed) cudaEventRecord(b->ev_stage[2], b->stream);
-        if (P.body_body) stage_manifold_kernel<<<st->grid_manifold, 128, st->smem_manifold, b->stream>>>(P);
+        if (P.body_body) st->manifold_fn<<<st->grid_manifold, kManifoldThreads, st->smem_manifold, b->stream>>>(P);
         if (timed) cudaEventRecord(b->ev_stage[3], b->stream);
         stage_solve_kernel<<<grid_solve, 128, 0, b->stream>>>(P);
         if (timed) cudaEventRecord(b->ev_stage[4], b->stream);
