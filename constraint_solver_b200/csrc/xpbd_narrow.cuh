@@ -33,7 +33,10 @@ XD V3 ld3(const float* a, int i) {
 }
 XD void st3(float* a, int i, V3 v) { reinterpret_cast<float4*>(a)[i] = make_float4(v.x, v.y, v.z, 0.0f); }
 constexpr int kVertWords = 4;      // words per vertex in those arrays
-constexpr int kEdgeQueueWords = 4 * 64;  // warp-private survivor queue of edge_query (axis.xyz, pair index)
+// warp-private scratch of edge_query: survivor queue (64 x (axis.xyz, pair index)) followed by the per-candidate
+// edge table of the compile-time-sized instantiation (edge vectors of A, their feet, edge vectors of B)
+constexpr int kEdgeTableMax = 36;
+constexpr int kEdgeQueueWords = 4 * (64 + kEdgeTableMax);
 
 // (value, index) arg-max across the warp: larger value wins, equal values -> lower index (the serial scan
 // keeps the FIRST strict maximum), index < 0 = "no candidate".  All lanes receive the result.
@@ -155,10 +158,25 @@ XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int 
     const int nA = NVA ? NVA : nA_rt, nB = NVB ? NVB : nB_rt;
     const int nEb = NEB ? NEB : nEb_rt, nPairs = (NEA ? NEA : nEa_rt) * nEb;
     float4* Q4v = reinterpret_cast<float4*>(Q);
+    // Small hulls: every edge vector is needed nEb (A) / nEa (B) times — compute each once per candidate.
+    constexpr bool kTable = NEA > 0 && NEB > 0 && NEA + NEB <= 32 && 2 * NEA + NEB <= kEdgeTableMax;
+    float* EV = Q + 4 * 64;  // [0, NEA) edge_a | [NEA, 2 NEA) foot | [2 NEA, 2 NEA + NEB) edge_b
+    if (kTable) {
+        if (lane < NEA) {
+            const int2 ea = EA[lane];
+            const V3 foot = ld3(WA, ea.x);
+            st3(EV, lane, ld3(WA, ea.y) - foot);
+            st3(EV, NEA + lane, foot);
+        } else if (lane < NEA + NEB) {
+            const int2 eb = EB[lane - NEA];
+            st3(EV, 2 * NEA + lane - NEA, ld3(WB, eb.y) - ld3(WB, eb.x));
+        }
+        __syncwarp();
+    }
     auto second_half = [&](float4 q) {
         const V3 axis = v3(q.x, q.y, q.z);
         const int e = __float_as_int(q.w);  // ia << 16 | jb: same order as the flat pair index
-        const V3 foot = ld3(WA, EA[e >> 16].x);
+        const V3 foot = kTable ? ld3(EV, NEA + (e >> 16)) : ld3(WA, EA[e >> 16].x);
         const float disp = plane_displacement(foot, axis);
         // plane.distance(B.support(-axis)) = min_v dot(axis, v) - displacement
         const float sb = NVB ? scan_dots_t<NVB, false>(WB, nB, axis) : scan_dots<false>(WB, nB, axis);
@@ -174,10 +192,15 @@ XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int 
         bool pass = false;
         V3 axis = v3(0.f, 0.f, 0.f);
         if (e0 + 32 <= nPairs || e < nPairs) {
-            const int2 ea = EA[ia], eb = EB[jb];
-            const V3 foot = ld3(WA, ea.x);
-            const V3 edge_a = ld3(WA, ea.y) - foot;
-            const V3 edge_b = ld3(WB, eb.y) - ld3(WB, eb.x);
+            V3 foot, edge_a, edge_b;
+            if (kTable) {
+                foot = ld3(EV, NEA + ia); edge_a = ld3(EV, ia); edge_b = ld3(EV, 2 * NEA + jb);
+            } else {
+                const int2 ea = EA[ia], eb = EB[jb];
+                foot = ld3(WA, ea.x);
+                edge_a = ld3(WA, ea.y) - foot;
+                edge_b = ld3(WB, eb.y) - ld3(WB, eb.x);
+            }
             axis = normalize(cross(edge_a, edge_b));  // parallel edges -> NaN axis, no guard (as the reference)
             if (dot(axis, foot - CA) < 0.0f) axis = -axis;
             // Ignore if another point on `a` is further in the direction to `b`.

@@ -41,7 +41,7 @@ struct StagedBuffers {
     int4* pairs = nullptr;    // per world x capP: (i | j << 16, feature, index, n_contacts)
     int* n_pairs = nullptr;   // per world
     float4* pcons = nullptr;  // per (world, pair slot) x kMaxManifold x 3 float4
-    int4* worklist = nullptr;  // per candidate: (world * capP + pair slot, i | j << 16, hull_i | hull_j << 16, 0)
+    int4* worklist = nullptr;  // per candidate: (world * capP + pair slot, i | j << 16, hull_i | hull_j << 16, world)
     uint32_t* work_count = nullptr;  // [0] candidates of this substep
     int* overflow = nullptr;         // per world
     int maxV = 0, capG = 0, capP = 0;
@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
             __syncwarp();  // the pair slots written above are read back by other lanes
             for (int p = gl; p < n_pairs; p += G) {
                 const int ij = pairs[p].x;
-                P.S.worklist[base + p] = make_int4((int)(world * P.S.capP + p), ij, s_hull[ij & 0xffff] | (s_hull[ij >> 16] << 16), 0);
+                P.S.worklist[base + p] = make_int4((int)(world * P.S.capP + p), ij, s_hull[ij & 0xffff] | (s_hull[ij >> 16] << 16), (int)world);
             }
         }
         overflow = (__ballot_sync(kFull, overflow) & gmask) != 0;
@@ -273,8 +273,8 @@ __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_kernel(Sta
     float* Q = W + 3 * kVertWords * maxV;
     const unsigned count = *P.S.work_count;
     for (unsigned it = blockIdx.x * nwarps + warp; it < count; it += gridDim.x * nwarps) {
-        const int4 d = P.S.worklist[it];  // slot, i | j << 16, hull_i | hull_j << 16: one load instead of a chain of three
-        const int64_t world = (uint32_t)d.x / (uint32_t)P.S.capP;
+        const int4 d = P.S.worklist[it];  // slot, i | j << 16, hull_i | hull_j << 16, world: one load instead of a chain of three
+        const int64_t world = d.w;
         const int64_t gi = world * B + (d.y & 0xffff), gj = world * B + (d.y >> 16);
         const HullDesc& hA = T.desc(d.z & 0xffff);
         const HullDesc& hB = T.desc(d.z >> 16);

@@ -9,6 +9,7 @@
 //     vertices, frames, candidate pairs, the edge query's survivor queue).  16-byte aligned: vertices are float4.
 #pragma once
 #include "xpbd_math.cuh"
+#include "xpbd_narrow.cuh"
 
 namespace xpbd {
 
@@ -54,7 +55,7 @@ __host__ __device__ inline WorldLayout make_world_layout(int B, int maxV, int ca
     auto take4 = [&](int words) { int r = o; o += (words + 3) & ~3; return r; };
     L.s_verts = take4(4 * maxV * B);
     L.s_local = take4(4 * maxV);
-    L.s_queue = take4(4 * 64);
+    L.s_queue = take4(kEdgeQueueWords);
     L.s_fpos = take4(3 * B); L.s_finvp = take4(3 * B); L.s_cen = take4(3 * B); L.s_pfpos = take4(3 * B);
     L.s_pairs = take4(3 * capP);
     L.sstride = o;
