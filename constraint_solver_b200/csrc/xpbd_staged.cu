@@ -258,7 +258,9 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
 #endif
 // (A cp.async double-buffered software pipeline over the work list was measured here and was SLOWER, 1.73 ms vs
 // 1.56 ms: the kernel is issue-slot bound with 32 resident warps per SM hiding the per-candidate load chain, and the
-// pipeline's extra address arithmetic and spills cost more than the exposed latency it removed.)
+// pipeline's extra address arithmetic and spills cost more than the exposed latency it removed.  A lighter look-ahead
+// — prefetch.global.L1 of the next candidate's seven input lines, one per lane, issued after the first face query —
+// was slower too: 1.57 ms vs 1.41 ms.)
 __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_kernel(StagedParams P) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ __align__(8) uint64_t bar;
