@@ -352,17 +352,17 @@ def main():
                 "share_of_step": stage_ms[1] / max(sum(stage_ms), 1e-9),
                 "step": line["roofline"],
                 "note": "dominant kernel of the staged pipeline, timed with CUDA events on the batch stream inside the library; "
-                        "FP32-issue bound (673 FP instructions of 1.8k per pair, DESIGN.md section 5), so the HBM fraction is small by construction",
+                        "FP32-issue bound (640 FADD/FMUL/FFMA of 1 340 warp-instructions per pair, DESIGN.md section 5), so the HBM fraction is small by construction",
             }
             if "fp32" in line["roofline"]["step"]:
                 line["roofline"]["fp32"] = line["roofline"]["step"].pop("fp32")
                 if args.workload == "c3":
-                    # FP32 work of one cube-cube candidate = 17 650 thread-level FADD/FMUL/FFMA instructions (ncu
-                    # smsp__sass_thread_inst_executed_op_f{add,mul,ffma}_pred_on of stage_sat_kernel, profiles/r01d_stage_sat.txt):
+                    # FP32 work of one cube-cube candidate = 17 630 thread-level flops (FADD + FMUL + 2 x FFMA, ncu SASS page
+                    # of stage_sat_kernel, profiles/r01g_stage_sat.txt / DESIGN.md section 5):
                     # the arithmetic of the reference's brute-force face + edge queries, nothing recomputed.
                     fp = line["roofline"]["fp32"]
-                    fp["flops_per_pair"] = 17650.0
-                    fp["achieved"] = cand_pairs * 17650.0 / (stage_ms[1] * 1e-3) / 1e12
+                    fp["flops_per_pair"] = 17630.0
+                    fp["achieved"] = cand_pairs * 17630.0 / (stage_ms[1] * 1e-3) / 1e12
                     fp["frac"] = fp["achieved"] / fp["peak"]
                     fp["kernel"] = "stage_sat_kernel"
         # roofline.traffic: DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/)
