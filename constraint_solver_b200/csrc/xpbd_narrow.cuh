@@ -36,7 +36,8 @@ constexpr int kVertWords = 4;      // words per vertex in those arrays
 // warp-private scratch of edge_query: survivor queue (64 x (axis.xyz, pair index)) followed by the per-candidate
 // edge table of the compile-time-sized instantiation (edge vectors of A, their feet, edge vectors of B)
 constexpr int kEdgeTableMax = 36;
-constexpr int kEdgeQueueWords = 4 * (64 + kEdgeTableMax);
+constexpr int kEdgeQueueWords = 4 * (64 + kEdgeTableMax);        // whole warp on one pair: 64-entry queue + table
+constexpr int kEdgeQueueWordsHalf = 4 * (32 + kEdgeTableMax);    // 16 lanes on one pair: 32-entry queue + table
 
 // (value, index) arg-max across the warp: larger value wins, equal values -> lower index (the serial scan
 // keeps the FIRST strict maximum), index < 0 = "no candidate".  All lanes receive the result.
@@ -44,19 +45,20 @@ constexpr int kEdgeQueueWords = 4 * (64 + kEdgeTableMax);
 // whose integer order is the float order (never NaN here: `best` is only ever assigned through `distance > best`;
 // -0 is folded into +0 first, which `>` cannot tell apart either), then the lowest index among the lanes that hold
 // the maximum is taken (an index of -1 is the largest unsigned value, so real candidates win).
-XD void warp_argmax_first(float& d, int& i) {
+XD void warp_argmax_first(float& d, int& i, unsigned mask = 0xffffffffu) {  // mask: the lane group that cooperates
     const uint32_t u = (uint32_t)__float_as_int(fadd(d, 0.0f));
     const uint32_t key = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-    const uint32_t m = __reduce_max_sync(0xffffffffu, key);
-    const uint32_t idx = __reduce_min_sync(0xffffffffu, key == m ? (uint32_t)i : 0xffffffffu);
+    const uint32_t m = __reduce_max_sync(mask, key);
+    const uint32_t idx = __reduce_min_sync(mask, key == m ? (uint32_t)i : 0xffffffffu);
     d = __int_as_float((int)((m & 0x80000000u) ? (m & 0x7fffffffu) : ~m));
     i = (int)idx;
 }
 
-// Support scans: extreme value of dot(axis, v) over the first n vertices of a float4 vertex array.  The common hull
-// sizes (tetrahedron 4, cube 8, icosahedron 12) get fully unrolled instantiations — no loop control, FMNMX3 pairs —
-// chosen by a warp-uniform switch; any other size takes the rolled loop.  min/max are exact, so the order in which
-// they are folded cannot change the value.
+// Support scans: extreme value of dot(axis, v) over the first n vertices of a float4 vertex array.  NV > 0: fully
+// unrolled (no loop control, FMNMX3 pairs) for the compile-time-sized instantiations; NV = 0: rolled loop over n.
+// (A warp-uniform switch to unrolled 4/8/12-vertex variants inside the generic path was removed again: in
+// mixed-hull batches the extra code cost more in instruction-cache misses than the unrolling saved, 1.72 vs 1.77 ms
+// on C4.)  min/max are exact, so the order in which they are folded cannot change the value.
 template <int NV, bool kMax>
 XD float scan_dots_t(const float* W, int n, V3 axis) {
     float s = dot(axis, ld3(W, 0));
@@ -69,14 +71,7 @@ XD float scan_dots_t(const float* W, int n, V3 axis) {
     return s;
 }
 template <bool kMax>
-XD float scan_dots(const float* W, int n, V3 axis) {
-    switch (n) {
-        case 4: return scan_dots_t<4, kMax>(W, n, axis);
-        case 8: return scan_dots_t<8, kMax>(W, n, axis);
-        case 12: return scan_dots_t<12, kMax>(W, n, axis);
-        default: return scan_dots_t<0, kMax>(W, n, axis);
-    }
-}
+XD float scan_dots(const float* W, int n, V3 axis) { return scan_dots_t<0, kMax>(W, n, axis); }
 
 // collision::face_axes_separation (src/collision.rs:123-149) for hull A's faces against hull B's vertices.
 // L: warp-private scratch for B's vertices in A-local space (float4 per vertex).
@@ -84,17 +79,19 @@ XD float scan_dots(const float* W, int n, V3 axis) {
 // G-th vertex and a shuffle-min butterfly across the groups completes the support value of every face
 // (cube vs cube: 4 groups x 2 vertices instead of 6 active lanes x 8 vertices).
 // NF / NB > 0: face / vertex counts known at compile time (the cube-cube instantiation), 0: taken from nF / nB.
-template <int NF, int NB>
+// LG = lanes that cooperate on one body pair: the whole warp, or 16 when a warp works on two pairs at once (then
+// `lane` is the lane's index inside its half and `gmask` the half's lane mask; every shuffle stays inside the half).
+template <int NF, int NB, int LG = 32>
 XD void face_query_t(const float4* planes, int nF_rt, const Fr& FinvA, const float* WB, int nB_rt, float* L, int lane,
-                     float& out_d, int& out_face) {
+                     float& out_d, int& out_face, unsigned gmask = 0xffffffffu) {
     const int nF = NF ? NF : nF_rt, nB = NB ? NB : nB_rt;
-    for (int v = lane; v < nB; v += 32) st3(L, v, FinvA * ld3(WB, v));  // frames.0.inverse() * (frames.1 * p)
-    __syncwarp();
+    for (int v = lane; v < nB; v += LG) st3(L, v, FinvA * ld3(WB, v));  // frames.0.inverse() * (frames.1 * p)
+    __syncwarp(gmask);
     float best = -FLT_MAX;  // f64::MIN
     int bi = -1;            // usize::MAX
     int nFp = 4;
-    while (nFp < nF && nFp < 32) nFp <<= 1;
-    int G = 32 / nFp;                 // lane groups
+    while (nFp < nF && nFp < LG) nFp <<= 1;
+    int G = LG / nFp;                 // lane groups
     while (G > nB) G >>= 1;           // every group must own at least one vertex
     if (G > 1) {
         const int f = lane & (nFp - 1), g = lane / nFp;
@@ -106,23 +103,23 @@ XD void face_query_t(const float4* planes, int nF_rt, const Fr& FinvA, const flo
             m = dot(n, ld3(L, g));
             for (int v = g + G; v < nB; v += G) m = fminf(m, dot(n, ld3(L, v)));
         }
-        for (int o = nFp; o < nFp * G; o <<= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        for (int o = nFp; o < nFp * G; o <<= 1) m = fminf(m, __shfl_xor_sync(gmask, m, o));
         if (f < nF && g == 0) {
             const float distance = fsub(m, pl.w);  // plane.distance(support)
             if (distance > best) { best = distance; bi = f; }
         }
     } else {
-        for (int f = lane; f < nF; f += 32) {
+        for (int f = lane; f < nF; f += LG) {
             const float4 pl = planes[f];
             const float m = scan_dots<false>(L, nB, v3(pl.x, pl.y, pl.z));
             const float distance = fsub(m, pl.w);
             if (distance > best) { best = distance; bi = f; }
         }
     }
-    warp_argmax_first(best, bi);
+    warp_argmax_first(best, bi, gmask);
     out_d = best;
     out_face = bi;
-    __syncwarp();
+    __syncwarp(gmask);
 }
 XD void face_query(const HullTable& T, const HullDesc& hA, const Fr& FinvA, const float* WB, int nB, float* L, int lane,
                    float& out_d, int& out_face) {
@@ -150,28 +147,35 @@ XD float plane_displacement(V3 point, V3 normal) {
 // Every value is computed by the same expression as before; only the schedule differs.
 // NVA/NEA/NVB/NEB > 0: vertex / edge counts known at compile time (the cube-cube instantiation: the pair loop is
 // unrolled, index arithmetic and support scans are straight-line code); 0: taken from the run-time arguments.
-template <int NVA, int NEA, int NVB, int NEB>
+// LG / gmask / gshift: lanes cooperating on this pair (see face_query_t); gshift = index of the group's first lane.
+// With LG = 16 two pairs share the warp and run this function in lockstep: the decision to drain the survivor queue
+// is then taken for both halves together (warp vote), each half draining what it has, so that the two halves
+// never serialise the expensive second half.
+template <int NVA, int NEA, int NVB, int NEB, int LG = 32>
 XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int nB_rt, int nEb_rt, const float* WA,
-                     const float* WB, V3 CA, float* Q, int lane, float& out_d, int& out_pair) {
+                     const float* WB, V3 CA, float* Q, int lane, float& out_d, int& out_pair,
+                     unsigned gmask = 0xffffffffu, int gshift = 0) {
     float best = -FLT_MAX;
     int bi = -1;
     const int nA = NVA ? NVA : nA_rt, nB = NVB ? NVB : nB_rt;
     const int nEb = NEB ? NEB : nEb_rt, nPairs = (NEA ? NEA : nEa_rt) * nEb;
-    float4* Q4v = reinterpret_cast<float4*>(Q);
+    float4* Q4v = reinterpret_cast<float4*>(Q);  // 2 LG entries
     // Small hulls: every edge vector is needed nEb (A) / nEa (B) times — compute each once per candidate.
-    constexpr bool kTable = NEA > 0 && NEB > 0 && NEA + NEB <= 32 && 2 * NEA + NEB <= kEdgeTableMax;
-    float* EV = Q + 4 * 64;  // [0, NEA) edge_a | [NEA, 2 NEA) foot | [2 NEA, 2 NEA + NEB) edge_b
+    constexpr bool kTable = NEA > 0 && NEB > 0 && 2 * NEA + NEB <= kEdgeTableMax;
+    float* EV = Q + 4 * 2 * LG;  // [0, NEA) edge_a | [NEA, 2 NEA) foot | [2 NEA, 2 NEA + NEB) edge_b
     if (kTable) {
-        if (lane < NEA) {
-            const int2 ea = EA[lane];
-            const V3 foot = ld3(WA, ea.x);
-            st3(EV, lane, ld3(WA, ea.y) - foot);
-            st3(EV, NEA + lane, foot);
-        } else if (lane < NEA + NEB) {
-            const int2 eb = EB[lane - NEA];
-            st3(EV, 2 * NEA + lane - NEA, ld3(WB, eb.y) - ld3(WB, eb.x));
+        for (int t = lane; t < NEA + NEB; t += LG) {
+            if (t < NEA) {
+                const int2 ea = EA[t];
+                const V3 foot = ld3(WA, ea.x);
+                st3(EV, t, ld3(WA, ea.y) - foot);
+                st3(EV, NEA + t, foot);
+            } else {
+                const int2 eb = EB[t - NEA];
+                st3(EV, NEA + t, ld3(WB, eb.y) - ld3(WB, eb.x));
+            }
         }
-        __syncwarp();
+        __syncwarp(gmask);
     }
     auto second_half = [&](float4 q) {
         const V3 axis = v3(q.x, q.y, q.z);
@@ -183,15 +187,27 @@ XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int 
         const float distance = fsub(sb, disp);
         if (distance > best || (distance == best && e < bi)) { best = distance; bi = e; }
     };
-    int qn = 0;  // warp-uniform
-    const int step_a = 32 / nEb, step_b = 32 - step_a * nEb;  // advancing the flat pair index by 32
+    int qn = 0;  // uniform across the lane group
+    const int step_a = LG / nEb, step_b = LG - step_a * nEb;  // advancing the flat pair index by LG
+    const unsigned below_me = (1u << lane) - 1u;
     int ia = lane / nEb, jb = lane - ia * nEb;
-#pragma unroll
-    for (int e0 = 0; e0 < nPairs; e0 += 32) {
+#ifndef XPBD_DUAL_UNROLL
+#define XPBD_DUAL_UNROLL 1
+#endif
+#ifndef XPBD_SINGLE_UNROLL
+#define XPBD_SINGLE_UNROLL 8
+#endif
+    // Code size matters here: the fully unrolled 16-lane loop measured 1.59 ms against 1.29 ms rolled (instruction
+    // cache), and in mixed-hull batches the rolled cube instantiation beats the unrolled one (1.81 vs 2.16 ms on C4).
+    // (Folding the final drain into the loop as an extra round, for a single call site of the second half, was
+    // slower: 1.35 vs 1.29 ms.)
+    constexpr int kUnroll = LG == 32 ? (NEA > 0 ? XPBD_SINGLE_UNROLL : 1) : XPBD_DUAL_UNROLL;
+#pragma unroll kUnroll
+    for (int e0 = 0; e0 < nPairs; e0 += LG) {
         const int e = e0 + lane;
         bool pass = false;
         V3 axis = v3(0.f, 0.f, 0.f);
-        if (e0 + 32 <= nPairs || e < nPairs) {
+        if (e0 + LG <= nPairs || e < nPairs) {
             V3 foot, edge_a, edge_b;
             if (kTable) {
                 foot = ld3(EV, NEA + ia); edge_a = ld3(EV, ia); edge_b = ld3(EV, 2 * NEA + jb);
@@ -207,21 +223,23 @@ XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int 
             const float sa = NVA ? scan_dots_t<NVA, true>(WA, nA, axis) : scan_dots<true>(WA, nA, axis);  // dot(v, axis) == dot(axis, v): IEEE multiplication commutes
             pass = !(sa > dot(foot, axis));
         }
-        const unsigned m = __ballot_sync(0xffffffffu, pass);
-        if (pass) Q4v[qn + __popc(m & ((1u << lane) - 1u))] = make_float4(axis.x, axis.y, axis.z, __int_as_float((ia << 16) | jb));
+        const unsigned m = __ballot_sync(gmask, pass) >> gshift;
+        if (pass) Q4v[qn + __popc(m & below_me)] = make_float4(axis.x, axis.y, axis.z, __int_as_float((ia << 16) | jb));
         ia += step_a; jb += step_b;
         if (jb >= nEb) { jb -= nEb; ++ia; }
         qn += __popc(m);
-        __syncwarp();
-        if (qn >= 32) {
-            qn -= 32;
-            second_half(Q4v[qn + lane]);
-            __syncwarp();
+        __syncwarp(gmask);
+        const bool drain = LG == 32 ? qn >= 32 : __any_sync(0xffffffffu, qn >= LG);
+        if (drain) {
+            const int take = qn < LG ? qn : LG;
+            qn -= take;
+            if (lane < take) second_half(Q4v[qn + lane]);
+            __syncwarp(gmask);
         }
     }
     if (lane < qn) second_half(Q4v[lane]);
-    __syncwarp();
-    warp_argmax_first(best, bi);
+    __syncwarp(gmask);
+    warp_argmax_first(best, bi, gmask);
     out_d = best;
     out_pair = bi < 0 ? -1 : (bi >> 16) * nEb + (bi & 0xffff);  // flat pair index ia * nEdgesB + jb
 }

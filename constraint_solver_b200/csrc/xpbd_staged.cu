@@ -261,46 +261,129 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
 // pipeline's extra address arithmetic and spills cost more than the exposed latency it removed.  A lighter look-ahead
 // — prefetch.global.L1 of the next candidate's seven input lines, one per lane, issued after the first face query —
 // was slower too: 1.57 ms vs 1.41 ms.)
+// per-warp shared scratch, in words: two sets of (WA, WB, L) + the queue/table region (two half-warp regions, which
+// together also hold the whole-warp layout)
+__host__ __device__ inline int sat_words_per_warp(int maxV) { return 6 * kVertWords * maxV + 2 * kEdgeQueueWordsHalf; }
+static_assert(2 * kEdgeQueueWordsHalf >= kEdgeQueueWords, "queue region must hold the whole-warp layout");
+
+XD bool is_cube_shape(const HullDesc& h) { return h.n_verts == 8 && h.n_edges == 12 && h.n_faces == 6; }
+
+// One candidate on the whole warp (any hull sizes).
+XD void sat_single(const StagedParams& P, const HullTable& T, int4 d, float* WA, float* WB, float* Lc, float* Q, int lane) {
+    const int B = P.B, maxV = P.S.maxV;
+    const int64_t world = d.w;
+    const int64_t gi = world * B + (d.y & 0xffff), gj = world * B + (d.y >> 16);
+    const HullDesc& hA = T.desc(d.z & 0xffff);
+    const HullDesc& hB = T.desc(d.z >> 16);
+    __syncwarp();
+    for (int v = lane; v < hA.n_verts; v += 32) reinterpret_cast<float4*>(WA)[v] = P.S.verts[gi * maxV + v];
+    for (int v = lane; v < hB.n_verts; v += 32) reinterpret_cast<float4*>(WB)[v] = P.S.verts[gj * maxV + v];
+    const float4 ra = P.bodies.dynC[gi], rb = P.bodies.dynC[gj];
+    const float4 fa4 = P.S.finvp[gi], fb4 = P.S.finvp[gj], ca4 = P.S.cen[gi];
+    Fr finvA, finvB;
+    finvA.q = conjugate(q4(ra.w, ra.x, ra.y, ra.z)); finvA.p = v3(fa4.x, fa4.y, fa4.z);
+    finvB.q = conjugate(q4(rb.w, rb.x, rb.y, rb.z)); finvB.p = v3(fb4.x, fb4.y, fb4.z);
+    __syncwarp();
+    float da, db = 0.f, de = 0.f;
+    int fa, fb = -1, ep = -1;
+    PairFeature pf; pf.feature = kNone; pf.index = -1;
+    // Generic instantiations only: all-cube batches run stage_sat_cubes_kernel, and in mixed batches the
+    // size-specialised code paths cost more in instruction-cache misses than they save (C4: 1.62 vs 1.77 ms).
+    const float4* planesA = reinterpret_cast<const float4*>(T.words + hA.plane_off);
+    const float4* planesB = reinterpret_cast<const float4*>(T.words + hB.plane_off);
+    face_query_t<0, 0>(planesA, hA.n_faces, finvA, WB, hB.n_verts, Lc, lane, da, fa);
+    if (!(da >= 0.0f)) {
+        face_query_t<0, 0>(planesB, hB.n_faces, finvB, WA, hA.n_verts, Lc, lane, db, fb);
+        if (!(db >= 0.0f)) {
+            const int2* EA = reinterpret_cast<const int2*>(T.words + hA.edge_off);
+            const int2* EB = reinterpret_cast<const int2*>(T.words + hB.edge_off);
+            edge_query_t<0, 0, 0, 0>(EA, EB, hA.n_verts, hA.n_edges, hB.n_verts, hB.n_edges, WA, WB, v3(ca4.x, ca4.y, ca4.z), Q,
+                                     lane, de, ep);
+            if (!(de >= 0.0f)) pf = choose_feature(da, fa, db, fb, de, ep);
+        }
+    }
+    if (lane == 0) { P.S.pairs[d.x].y = pf.feature; P.S.pairs[d.x].z = pf.index; }
+}
+
+// Two cube-cube candidates on one warp, 16 lanes each, in lockstep: the 144 edge pairs of a cube pair fill 4.5
+// rounds of 32 lanes but exactly 9 rounds of 16, the face queries use 16 of 16 lanes instead of 24 of 32, and the
+// per-candidate setup (descriptor, vertices, frames, edge table) is issued once for both.  Each half runs exactly
+// the single-candidate arithmetic on its own scratch; the queries are entered by both halves together (a half whose
+// candidate is already separated idles through them) so that the warp never serialises the two halves.
+XD void sat_dual_cubes(const StagedParams& P, const HullTable& T, int4 d, bool valid, float* W, float* Qregion, int lane) {
+    const int B = P.B, maxV = P.S.maxV;
+    const int half = lane >> 4, hl = lane & 15, gshift = half * 16;
+    const unsigned gmask = 0xffffu << gshift;
+    float* WA = W + half * 3 * kVertWords * maxV; float* WB = WA + kVertWords * maxV; float* Lc = WB + kVertWords * maxV;
+    float* Q = Qregion + half * kEdgeQueueWordsHalf;
+    const int64_t world = d.w;
+    const int64_t gi = world * B + (d.y & 0xffff), gj = world * B + (d.y >> 16);
+    const HullDesc& hA = T.desc(d.z & 0xffff);
+    const HullDesc& hB = T.desc(d.z >> 16);
+    __syncwarp();
+    float4 ra, rb, fa4, fb4, ca4;
+    ra = rb = fa4 = fb4 = ca4 = make_float4(0.f, 0.f, 0.f, 1.f);
+    if (valid) {  // an odd work list leaves the last warp's second half without a candidate: it idles through
+        if (hl < 8) reinterpret_cast<float4*>(WA)[hl] = P.S.verts[gi * maxV + hl];
+        else reinterpret_cast<float4*>(WB)[hl - 8] = P.S.verts[gj * maxV + hl - 8];
+        ra = P.bodies.dynC[gi]; rb = P.bodies.dynC[gj];
+        fa4 = P.S.finvp[gi]; fb4 = P.S.finvp[gj]; ca4 = P.S.cen[gi];
+    }
+    Fr finvA, finvB;
+    finvA.q = conjugate(q4(ra.w, ra.x, ra.y, ra.z)); finvA.p = v3(fa4.x, fa4.y, fa4.z);
+    finvB.q = conjugate(q4(rb.w, rb.x, rb.y, rb.z)); finvB.p = v3(fb4.x, fb4.y, fb4.z);
+    __syncwarp();
+    const float4* planesA = reinterpret_cast<const float4*>(T.words + hA.plane_off);
+    const float4* planesB = reinterpret_cast<const float4*>(T.words + hB.plane_off);
+    float da, db = 0.f, de = 0.f;
+    int fa, fb = -1, ep = -1;
+    PairFeature pf; pf.feature = kNone; pf.index = -1;
+    face_query_t<6, 8, 16>(planesA, 6, finvA, WB, 8, Lc, hl, da, fa, gmask);
+    bool open = valid && !(da >= 0.0f);  // this half's candidate still needs the next query
+    if (__any_sync(0xffffffffu, open)) {
+        face_query_t<6, 8, 16>(planesB, 6, finvB, WA, 8, Lc, hl, db, fb, gmask);
+        open = open && !(db >= 0.0f);
+        if (__any_sync(0xffffffffu, open)) {
+            const int2* EA = reinterpret_cast<const int2*>(T.words + hA.edge_off);
+            const int2* EB = reinterpret_cast<const int2*>(T.words + hB.edge_off);
+            edge_query_t<8, 12, 8, 12, 16>(EA, EB, 8, 12, 8, 12, WA, WB, v3(ca4.x, ca4.y, ca4.z), Q, hl, de, ep, gmask, gshift);
+            if (open && !(de >= 0.0f)) pf = choose_feature(da, fa, db, fb, de, ep);
+        }
+    }
+    if (hl == 0 && valid) { P.S.pairs[d.x].y = pf.feature; P.S.pairs[d.x].z = pf.index; }
+}
+
 __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_kernel(StagedParams P) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ __align__(8) uint64_t bar;
     stage_bulk(smem, P.hull_blob, P.hull_blob_bytes, &bar, reinterpret_cast<unsigned int*>(P.counters + 2));
     const HullTable T{smem};
-    const int B = P.B, maxV = P.S.maxV;
+    const int maxV = P.S.maxV;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    // per-warp scratch: WA, WB, L (float4 x maxV each), survivor queue
-    const int per_warp = 3 * kVertWords * maxV + kEdgeQueueWords;
-    float* W = reinterpret_cast<float*>(smem) + P.hull_blob_bytes / 4 + (size_t)warp * per_warp;
-    float* WA = W; float* WB = W + kVertWords * maxV; float* Lc = W + 2 * kVertWords * maxV;
-    float* Q = W + 3 * kVertWords * maxV;
+    float* W = reinterpret_cast<float*>(smem) + P.hull_blob_bytes / 4 + (size_t)warp * sat_words_per_warp(maxV);
+    float* Qregion = W + 6 * kVertWords * maxV;
     const unsigned count = *P.S.work_count;
-    for (unsigned it = blockIdx.x * nwarps + warp; it < count; it += gridDim.x * nwarps) {
-        const int4 d = P.S.worklist[it];  // slot, i | j << 16, hull_i | hull_j << 16, world: one load instead of a chain of three
-        const int64_t world = d.w;
-        const int64_t gi = world * B + (d.y & 0xffff), gj = world * B + (d.y >> 16);
-        const HullDesc& hA = T.desc(d.z & 0xffff);
-        const HullDesc& hB = T.desc(d.z >> 16);
-        __syncwarp();
-        for (int v = lane; v < hA.n_verts; v += 32) reinterpret_cast<float4*>(WA)[v] = P.S.verts[gi * maxV + v];
-        for (int v = lane; v < hB.n_verts; v += 32) reinterpret_cast<float4*>(WB)[v] = P.S.verts[gj * maxV + v];
-        const float4 ra = P.bodies.dynC[gi], rb = P.bodies.dynC[gj];
-        const float4 fa4 = P.S.finvp[gi], fb4 = P.S.finvp[gj], ca4 = P.S.cen[gi];
-        Fr finvA, finvB;
-        finvA.q = conjugate(q4(ra.w, ra.x, ra.y, ra.z)); finvA.p = v3(fa4.x, fa4.y, fa4.z);
-        finvB.q = conjugate(q4(rb.w, rb.x, rb.y, rb.z)); finvB.p = v3(fb4.x, fb4.y, fb4.z);
-        __syncwarp();
-        float da, db = 0.f, de = 0.f;
-        int fa, fb = -1, ep = -1;
-        PairFeature pf; pf.feature = kNone; pf.index = -1;
-        face_query(T, hA, finvA, WB, hB.n_verts, Lc, lane, da, fa);
-        if (!(da >= 0.0f)) {
-            face_query(T, hB, finvB, WA, hA.n_verts, Lc, lane, db, fb);
-            if (!(db >= 0.0f)) {
-                edge_query(T, hA, hB, WA, WB, v3(ca4.x, ca4.y, ca4.z), Q, lane, de, ep);
-                if (!(de >= 0.0f)) pf = choose_feature(da, fa, db, fb, de, ep);
-            }
-        }
-        if (lane == 0) { P.S.pairs[d.x].y = pf.feature; P.S.pairs[d.x].z = pf.index; }
+    for (unsigned it = blockIdx.x * nwarps + warp; it < count; it += gridDim.x * nwarps)
+        sat_single(P, T, P.S.worklist[it], W, W + kVertWords * maxV, W + 2 * kVertWords * maxV, Qregion, lane);
+}
+
+// Batches in which every registered hull is cube-shaped (8 vertices, 12 edges, 6 quads): two candidates per warp.
+__global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_cubes_kernel(StagedParams P) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    __shared__ __align__(8) uint64_t bar;
+    stage_bulk(smem, P.hull_blob, P.hull_blob_bytes, &bar, reinterpret_cast<unsigned int*>(P.counters + 2));
+    const HullTable T{smem};
+    const int maxV = P.S.maxV;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    float* W = reinterpret_cast<float*>(smem) + P.hull_blob_bytes / 4 + (size_t)warp * sat_words_per_warp(maxV);
+    float* Qregion = W + 6 * kVertWords * maxV;
+    const unsigned count = *P.S.work_count;
+    for (unsigned it = 2 * (blockIdx.x * nwarps + warp); it < count; it += 2 * gridDim.x * nwarps) {
+        const unsigned mine = it + (lane >> 4);
+        const bool valid = mine < count;
+        int4 d = make_int4(0, 0, 0, 0);
+        if (valid) d = P.S.worklist[mine];  // slot, i | j << 16, hull_i | hull_j << 16, world
+        sat_dual_cubes(P, T, d, valid, W, Qregion, lane);
     }
 }
 
@@ -565,6 +648,7 @@ __global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel
 struct StagedState {
     StagedBuffers buf;
     int64_t n_worlds = 0;
+    size_t n_hulls = 0;  // kernel choices depend on the registered hulls
     int B = 0;
     int grid_prepare = 0, grid_sat = 0, grid_manifold = 0;
     size_t smem_prepare = 0, smem_sat = 0, smem_manifold = 0;
@@ -572,6 +656,7 @@ struct StagedState {
     int clip_cap = kMaxClip;
     void (*manifold_fn)(StagedParams) = nullptr;
     void (*prepare_fn)(StagedParams) = nullptr;
+    void (*sat_fn)(StagedParams) = nullptr;
     int prepare_lanes = 32, pair_table_len = 0;
     int n_sm = 148;
     int solve_blocks_per_sm = 0;  // grid-stride over worlds: resident blocks per SM (occupancy), XPBD_SOLVE_BLOCKS_PER_SM overrides
@@ -596,12 +681,13 @@ static int ensure_staged(xpbd_batch* b, StagedState*& out) {
     const int B = b->desc.bodies_per_world;
     const DeviceHulls& H = b->dev_hulls;
     StagedState* st = static_cast<StagedState*>(b->world_scratch);
-    if (st && st->buf.maxV == H.max_verts) { out = st; return XPBD_OK; }
+    if (st && st->buf.maxV == H.max_verts && st->n_hulls == b->hulls.size()) { out = st; return XPBD_OK; }
     release_world_scratch(b);
     st = new StagedState();
     b->world_scratch = st;
     st->n_worlds = b->desc.n_worlds;
     st->B = B;
+    st->n_hulls = b->hulls.size();
     StagedBuffers& S = st->buf;
     S.maxV = H.max_verts;
     S.capG = 8 * B < B * S.maxV ? 8 * B : B * S.maxV;
@@ -645,20 +731,31 @@ static int ensure_staged(xpbd_batch* b, StagedState*& out) {
     while (wp > 1 && H.bytes + wp * prep_per_warp + table_bytes > (size_t)smem_max / 2) wp >>= 1;
     st->warps_prepare = wp;
     st->smem_prepare = H.bytes + wp * prep_per_warp + table_bytes;
-    st->smem_sat = H.bytes + 8 * (size_t)(3 * kVertWords * S.maxV + kEdgeQueueWords) * 4;
+    st->smem_sat = H.bytes + 8 * (size_t)sat_words_per_warp(S.maxV) * 4;
     st->clip_cap = 2 * H.max_face_verts <= 8 ? 8 : kMaxClip;  // entries per clip buffer in stage_manifold's scratch
     st->smem_manifold = H.bytes + (size_t)kManifoldThreads * 7 * st->clip_cap * 4;
     if (st->smem_prepare > (size_t)smem_max || st->smem_sat > (size_t)smem_max || st->smem_manifold > (size_t)smem_max)
         return fail(XPBD_ERR_CAPACITY, "hull table / world too large for shared memory (%zu, %zu bytes)", st->smem_prepare, st->smem_sat);
     XPBD_CUDA_TRY(cudaFuncSetAttribute(st->prepare_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_prepare));
-    XPBD_CUDA_TRY(cudaFuncSetAttribute(stage_sat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_sat));
+    st->sat_fn = stage_sat_kernel;
+    {
+        bool all_cubes = !b->hulls.empty();
+        for (const HostHull& h : b->hulls) {
+            bool quads = h.face_offsets.size() == 7;
+            for (size_t f = 0; quads && f + 1 < h.face_offsets.size(); ++f) quads = h.face_offsets[f + 1] - h.face_offsets[f] == 4;
+            all_cubes = all_cubes && h.vertices.size() == 8 * 3 && h.edges.size() == 12 * 2 && quads;
+        }
+        const char* e = std::getenv("XPBD_SAT_DUAL");
+        if (all_cubes && !(e && e[0] == '0')) st->sat_fn = stage_sat_cubes_kernel;
+    }
+    XPBD_CUDA_TRY(cudaFuncSetAttribute(st->sat_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_sat));
     st->manifold_fn = st->clip_cap == 8 ? stage_manifold_kernel<8> : stage_manifold_kernel<kMaxClip>;
     XPBD_CUDA_TRY(cudaFuncSetAttribute(st->manifold_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_manifold));
     int occ = 1;
     XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, st->prepare_fn, 32 * wp, st->smem_prepare));
     const int64_t worlds_per_block = (int64_t)wp * (32 / st->prepare_lanes);
     st->grid_prepare = (int)std::min<int64_t>((b->desc.n_worlds + worlds_per_block - 1) / worlds_per_block, (int64_t)n_sm * (occ > 0 ? occ : 1));
-    XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, stage_sat_kernel, 256, st->smem_sat));
+    XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, st->sat_fn, 256, st->smem_sat));
     st->grid_sat = (int)std::min<int64_t>(((int64_t)nw * S.capP + 7) / 8, (int64_t)n_sm * (occ > 0 ? occ : 1));
     XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, st->manifold_fn, kManifoldThreads, st->smem_manifold));
     st->grid_manifold = (int)std::min<int64_t>(((int64_t)nw * S.capP + 127) / 128, (int64_t)n_sm * (occ > 0 ? occ : 1));
@@ -705,7 +802,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
         if (timed) cudaEventRecord(b->ev_stage[0], b->stream);
         st->prepare_fn<<<st->grid_prepare, 32 * st->warps_prepare, st->smem_prepare, b->stream>>>(P);
         if (timed) cudaEventRecord(b->ev_stage[1], b->stream);
-        if (P.body_body) stage_sat_kernel<<<st->grid_sat, 256, st->smem_sat, b->stream>>>(P);
+        if (P.body_body) st->sat_fn<<<st->grid_sat, 256, st->smem_sat, b->stream>>>(P);
         if (timed) cudaEventRecord(b->ev_stage[2], b->stream);
         if (P.body_body) st->manifold_fn<<<st->grid_manifold, kManifoldThreads, st->smem_manifold, b->stream>>>(P);
         if (timed) cudaEventRecord(b->ev_stage[3], b->stream);

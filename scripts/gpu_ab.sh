@@ -16,7 +16,7 @@ for e in "${ENVS[@]}"; do [ -n "$e" ] && { echo "== env $e"; env $e bash -c "$(d
 cp $L/libxpbd_b200.so /tmp/keep.so
 for v in $L/variants/*.so; do
   [ -f "$v" ] || continue
-  echo "== variant $(basename $v .so)"; cp "$v" $L/libxpbd_b200.so; run
+  echo "== variant $(basename $v .so) ${AB_VARIANT_ENV:-}"; cp "$v" $L/libxpbd_b200.so; env ${AB_VARIANT_ENV:-} bash -c "$(declare -f run); run"
 done
 cp /tmp/keep.so $L/libxpbd_b200.so
 if [ "${AB_TESTS:-1}" = 1 ]; then
