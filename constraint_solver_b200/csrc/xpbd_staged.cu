@@ -585,8 +585,9 @@ __global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel
             // --- ... then the manifolds of the candidate pairs i<j in lexicographic order ...
             for (int p = 0; p < n_pairs; ++p) {
                 const int cnt = pairs[p].w;
+                int active_mask = 0;  // contacts of this manifold that were active, for the velocity pass
                 for (int k = 0; k < cnt; ++k) {
-                    float4* c = pc + ((size_t)p * kMaxManifold + k) * 3;
+                    const float4* c = pc + ((size_t)p * kMaxManifold + k) * 3;
                     const float4 c0 = c[0], c1 = c[1], c2 = c[2];
                     const int head = __float_as_int(c0.x);
                     const int role = contact_role(side, head);
@@ -594,8 +595,11 @@ __global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel
                     C.release(me); __syncwarp(pm); C.acquire(me);
                     const bool active = solve_contact(C, role, pm, me, role ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w),
                                                       v3(c2.x, c2.y, c2.z), sc);
-                    if (active && role == 0) c[0].x = __int_as_float(head | kActiveBit);
+                    active_mask |= (int)active << k;
                 }
+                // one 4-byte store per pair (stage_manifold rewrites the word every substep) instead of a flag in every
+                // contact record: those were four scattered 32-byte sector writes per pair
+                if (side == 0 && active_mask) pairs[p].w = cnt | (active_mask << 8);
                 applied += cnt;
             }
             // --- ... then the joints in index order
@@ -619,14 +623,13 @@ __global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel
         {
             CachedBody<true> C{P.bodies, world * P.B};
             for (int p = 0; p < n_pairs; ++p) {
-                const int cnt = pairs[p].w;
+                const int word = pairs[p].w, cnt = word & 0xff, active_mask = word >> 8;
                 for (int k = 0; k < cnt; ++k) {
+                    if (!((active_mask >> k) & 1)) continue;
                     const float4* c = pc + ((size_t)p * kMaxManifold + k) * 3;
-                    const float4 c0 = c[0];
+                    const float4 c0 = c[0], c1 = c[1], c2 = c[2];
                     const int head = __float_as_int(c0.x);
-                    if (!(head & kActiveBit)) continue;
-                    const float4 c1 = c[1], c2 = c[2];
-                    const int role = contact_role(side, head & ~kActiveBit);
+                    const int role = contact_role(side, head);
                     const int me = role ? head_b(head) : head_a(head);
                     C.release(me); __syncwarp(pm); C.acquire(me);
                     velocity_contact(C, role, pm, me, role ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w), v3(c2.x, c2.y, c2.z),
