@@ -336,7 +336,9 @@ def main():
                 fp["algorithmic_flops_per_launch"] = flops
             line["roofline"]["fp32"] = fp
         if stage_ms is not None and stage_ms[1] > 0:
-            # Dominant kernel of the multi-body pipeline: stage_sat_kernel (one warp per candidate body pair).
+            # Dominant kernel of the multi-body pipeline: the SAT stage — stage_sat_cubes_kernel (two cube-cube candidates per
+            # warp) when every hull of the batch is cube-shaped (C3/C5), else stage_sat_kernel (one warp per candidate pair).
+            sat_kernel = "stage_sat_cubes_kernel" if args.workload == "c3" else "stage_sat_kernel"
             # Algorithmic bytes per pair: world-space vertices of both hulls (12 B each), two rotations (16 B each), two
             # inverse-frame positions and the centroid of A (12 B each), the pair record (16 B read + 8 B written).
             mean_verts = float(np.mean([len(h.vertices) for h in hulls])) if "hull_ids" not in extras else \
@@ -344,7 +346,7 @@ def main():
             bytes_per_pair = 2 * 12.0 * mean_verts + 2 * 16 + 3 * 12 + 24
             sat_gbs = cand_pairs * bytes_per_pair / (stage_ms[1] * 1e-3) / 1e9
             line["roofline"] = {
-                "bound": "hbm", "kernel": "stage_sat_kernel", "achieved": sat_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "bound": "hbm", "kernel": sat_kernel, "achieved": sat_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": sat_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_kind,
                 "algorithmic_bytes_per_launch": cand_pairs * bytes_per_pair, "kernel_ms": stage_ms[1],
                 "candidate_pairs_per_launch": cand_pairs, "bytes_per_pair": bytes_per_pair,
@@ -352,19 +354,19 @@ def main():
                 "share_of_step": stage_ms[1] / max(sum(stage_ms), 1e-9),
                 "step": line["roofline"],
                 "note": "dominant kernel of the staged pipeline, timed with CUDA events on the batch stream inside the library; "
-                        "FP32-issue bound (640 FADD/FMUL/FFMA of 1 340 warp-instructions per pair, DESIGN.md section 5), so the HBM fraction is small by construction",
+                        "FP32-issue bound (C3: 569 FADD/FMUL/FFMA of 1 274 warp-instructions per pair, DESIGN.md section 5), so the HBM fraction is small by construction",
             }
             if "fp32" in line["roofline"]["step"]:
                 line["roofline"]["fp32"] = line["roofline"]["step"].pop("fp32")
                 if args.workload == "c3":
-                    # FP32 work of one cube-cube candidate = 17 630 thread-level flops (FADD + FMUL + 2 x FFMA, ncu SASS page
-                    # of stage_sat_kernel, profiles/r01g_stage_sat.txt / DESIGN.md section 5):
+                    # FP32 work of one cube-cube candidate = 17 480 thread-level flops (FADD + FMUL + 2 x FFMA, ncu SASS page
+                    # of stage_sat_cubes_kernel, profiles/r01h_stage_sat_cubes.txt / DESIGN.md section 5):
                     # the arithmetic of the reference's brute-force face + edge queries, nothing recomputed.
                     fp = line["roofline"]["fp32"]
-                    fp["flops_per_pair"] = 17630.0
-                    fp["achieved"] = cand_pairs * 17630.0 / (stage_ms[1] * 1e-3) / 1e12
+                    fp["flops_per_pair"] = 17480.0
+                    fp["achieved"] = cand_pairs * 17480.0 / (stage_ms[1] * 1e-3) / 1e12
                     fp["frac"] = fp["achieved"] / fp["peak"]
-                    fp["kernel"] = "stage_sat_kernel"
+                    fp["kernel"] = sat_kernel
         # roofline.traffic: DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/)
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:

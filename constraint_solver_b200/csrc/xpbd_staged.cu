@@ -391,7 +391,10 @@ __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_cubes_kern
 #ifndef XPBD_MANIFOLD_MIN_BLOCKS
 #define XPBD_MANIFOLD_MIN_BLOCKS 4
 #endif
-constexpr int kManifoldThreads = 128;
+#ifndef XPBD_MANIFOLD_THREADS
+#define XPBD_MANIFOLD_THREADS 128
+#endif
+constexpr int kManifoldThreads = XPBD_MANIFOLD_THREADS;
 template <int CAP>
 __global__ void __launch_bounds__(kManifoldThreads, XPBD_MANIFOLD_MIN_BLOCKS) stage_manifold_kernel(StagedParams P) {
     extern __shared__ __align__(16) uint32_t smem[];
