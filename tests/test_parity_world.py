@@ -121,6 +121,27 @@ def test_tumbling_pile_of_mixed_hulls():
     assert c["manifolds"] > 1000
 
 
+def test_tumbling_pile_of_cubes_and_boxes():
+    """All hulls cube-shaped (a unit cube and a scaled box): on the staged path this is the two-pairs-per-warp SAT
+    kernel, with separated candidates, edge-edge contacts, an odd world count and odd candidate counts (one half of
+    the last warp idles)."""
+    hulls = [CUBE, CUBE.scaled(0.7)]
+    n, B = 51, 5
+    rng = np.random.default_rng(11)
+    init = np.empty((n, B), dtype=_abi.RIGID_DTYPE)
+    ids = rng.integers(0, 2, (n, B)).astype(np.int32)
+    for k, h in enumerate(hulls):
+        r = cs.Rigid(h.rigid_metrics(0.5))
+        r.external_force = (0.0, 0.0, -10.0 / r.inverse_mass)
+        init[ids == k] = r.rec
+    init["position"][:, :, 0:2] = rng.uniform(-0.4, 0.4, (n, B, 2))
+    init["position"][:, :, 2] = 0.5 + 1.5 * np.arange(B)[None, :] + rng.uniform(0, 0.2, (n, B))  # no initial overlap
+    init["rotation"] = scenes.random_unit_quaternions(rng, n * B).reshape(n, B, 4)
+    init["angular_velocity"] = rng.uniform(-2, 2, (n, B, 3))
+    _, c = _check(init, hulls, 120, 20, hull_ids=ids)
+    assert c["manifolds"] > 5000 and c["pairs_tested"] > c["manifolds"]  # contacts and separated candidates
+
+
 def test_joints_chain_without_body_contacts():
     """Distance joints (Constraint.distance, src/constraint.rs:9): a hanging chain of cubes, one end pinned to the world."""
     n, B = 48, 5
