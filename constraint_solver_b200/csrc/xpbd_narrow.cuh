@@ -54,6 +54,23 @@ XD void warp_argmax_first(float& d, int& i, unsigned mask = 0xffffffffu) {  // m
     i = (int)idx;
 }
 
+// The same for two 16-lane groups that run in lockstep (gshift = 0 for lanes 0-15, 16 for lanes 16-31): four
+// full-mask reductions in which each half contributes the neutral element to the other half's reduction.  (Reductions
+// with a run-time partial mask compile to MATCH-based loops: ~3x the instructions.)
+XD void warp_argmax_first_halves(float& d, int& i, int gshift) {
+    const uint32_t u = (uint32_t)__float_as_int(fadd(d, 0.0f));
+    const uint32_t key = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    const bool hi = gshift != 0;
+    const uint32_t m_lo = __reduce_max_sync(0xffffffffu, hi ? 0u : key);
+    const uint32_t m_hi = __reduce_max_sync(0xffffffffu, hi ? key : 0u);
+    const uint32_t m = hi ? m_hi : m_lo;
+    const uint32_t cand = key == m ? (uint32_t)i : 0xffffffffu;
+    const uint32_t i_lo = __reduce_min_sync(0xffffffffu, hi ? 0xffffffffu : cand);
+    const uint32_t i_hi = __reduce_min_sync(0xffffffffu, hi ? cand : 0xffffffffu);
+    d = __int_as_float((int)((m & 0x80000000u) ? (m & 0x7fffffffu) : ~m));
+    i = (int)(hi ? i_hi : i_lo);
+}
+
 // Support scans: extreme value of dot(axis, v) over the first n vertices of a float4 vertex array.  NV > 0: fully
 // unrolled (no loop control, FMNMX3 pairs) for the compile-time-sized instantiations; NV = 0: rolled loop over n.
 // (A warp-uniform switch to unrolled 4/8/12-vertex variants inside the generic path was removed again: in
@@ -79,14 +96,16 @@ XD float scan_dots(const float* W, int n, V3 axis) { return scan_dots_t<0, kMax>
 // G-th vertex and a shuffle-min butterfly across the groups completes the support value of every face
 // (cube vs cube: 4 groups x 2 vertices instead of 6 active lanes x 8 vertices).
 // NF / NB > 0: face / vertex counts known at compile time (the cube-cube instantiation), 0: taken from nF / nB.
-// LG = lanes that cooperate on one body pair: the whole warp, or 16 when a warp works on two pairs at once (then
-// `lane` is the lane's index inside its half and `gmask` the half's lane mask; every shuffle stays inside the half).
+// LG = lanes that cooperate on one body pair: the whole warp, or 16 when a warp works on two pairs at once.  Then
+// `lane` is the lane's index inside its half, gshift the index of the half's first lane, and the two halves MUST call
+// this function together (lockstep): every sync, shuffle and vote names the full warp, shuffles stay inside a half
+// because their xor distance is < 16.
 template <int NF, int NB, int LG = 32>
 XD void face_query_t(const float4* planes, int nF_rt, const Fr& FinvA, const float* WB, int nB_rt, float* L, int lane,
-                     float& out_d, int& out_face, unsigned gmask = 0xffffffffu) {
+                     float& out_d, int& out_face, int gshift = 0) {
     const int nF = NF ? NF : nF_rt, nB = NB ? NB : nB_rt;
     for (int v = lane; v < nB; v += LG) st3(L, v, FinvA * ld3(WB, v));  // frames.0.inverse() * (frames.1 * p)
-    __syncwarp(gmask);
+    __syncwarp();
     float best = -FLT_MAX;  // f64::MIN
     int bi = -1;            // usize::MAX
     int nFp = 4;
@@ -103,7 +122,7 @@ XD void face_query_t(const float4* planes, int nF_rt, const Fr& FinvA, const flo
             m = dot(n, ld3(L, g));
             for (int v = g + G; v < nB; v += G) m = fminf(m, dot(n, ld3(L, v)));
         }
-        for (int o = nFp; o < nFp * G; o <<= 1) m = fminf(m, __shfl_xor_sync(gmask, m, o));
+        for (int o = nFp; o < nFp * G; o <<= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
         if (f < nF && g == 0) {
             const float distance = fsub(m, pl.w);  // plane.distance(support)
             if (distance > best) { best = distance; bi = f; }
@@ -116,10 +135,10 @@ XD void face_query_t(const float4* planes, int nF_rt, const Fr& FinvA, const flo
             if (distance > best) { best = distance; bi = f; }
         }
     }
-    warp_argmax_first(best, bi, gmask);
+    if (LG == 32) warp_argmax_first(best, bi); else warp_argmax_first_halves(best, bi, gshift);
     out_d = best;
     out_face = bi;
-    __syncwarp(gmask);
+    __syncwarp();
 }
 XD void face_query(const HullTable& T, const HullDesc& hA, const Fr& FinvA, const float* WB, int nB, float* L, int lane,
                    float& out_d, int& out_face) {
@@ -147,14 +166,14 @@ XD float plane_displacement(V3 point, V3 normal) {
 // Every value is computed by the same expression as before; only the schedule differs.
 // NVA/NEA/NVB/NEB > 0: vertex / edge counts known at compile time (the cube-cube instantiation: the pair loop is
 // unrolled, index arithmetic and support scans are straight-line code); 0: taken from the run-time arguments.
-// LG / gmask / gshift: lanes cooperating on this pair (see face_query_t); gshift = index of the group's first lane.
+// LG / gshift: lanes cooperating on this pair (see face_query_t); gshift = index of the group's first lane.
 // With LG = 16 two pairs share the warp and run this function in lockstep: the decision to drain the survivor queue
 // is then taken for both halves together (warp vote), each half draining what it has, so that the two halves
 // never serialise the expensive second half.
 template <int NVA, int NEA, int NVB, int NEB, int LG = 32>
 XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int nB_rt, int nEb_rt, const float* WA,
                      const float* WB, V3 CA, float* Q, int lane, float& out_d, int& out_pair,
-                     unsigned gmask = 0xffffffffu, int gshift = 0) {
+                     int gshift = 0) {
     float best = -FLT_MAX;
     int bi = -1;
     const int nA = NVA ? NVA : nA_rt, nB = NVB ? NVB : nB_rt;
@@ -175,7 +194,7 @@ XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int 
                 st3(EV, NEA + t, ld3(WB, eb.y) - ld3(WB, eb.x));
             }
         }
-        __syncwarp(gmask);
+        __syncwarp();
     }
     auto second_half = [&](float4 q) {
         const V3 axis = v3(q.x, q.y, q.z);
@@ -223,23 +242,23 @@ XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int 
             const float sa = NVA ? scan_dots_t<NVA, true>(WA, nA, axis) : scan_dots<true>(WA, nA, axis);  // dot(v, axis) == dot(axis, v): IEEE multiplication commutes
             pass = !(sa > dot(foot, axis));
         }
-        const unsigned m = __ballot_sync(gmask, pass) >> gshift;
+        const unsigned m = LG == 32 ? __ballot_sync(0xffffffffu, pass) : ((__ballot_sync(0xffffffffu, pass) >> gshift) & ((1u << (LG & 31)) - 1u));
         if (pass) Q4v[qn + __popc(m & below_me)] = make_float4(axis.x, axis.y, axis.z, __int_as_float((ia << 16) | jb));
         ia += step_a; jb += step_b;
         if (jb >= nEb) { jb -= nEb; ++ia; }
         qn += __popc(m);
-        __syncwarp(gmask);
+        __syncwarp();
         const bool drain = LG == 32 ? qn >= 32 : __any_sync(0xffffffffu, qn >= LG);
         if (drain) {
             const int take = qn < LG ? qn : LG;
             qn -= take;
             if (lane < take) second_half(Q4v[qn + lane]);
-            __syncwarp(gmask);
+            __syncwarp();
         }
     }
     if (lane < qn) second_half(Q4v[lane]);
-    __syncwarp(gmask);
-    warp_argmax_first(best, bi, gmask);
+    __syncwarp();
+    if (LG == 32) warp_argmax_first(best, bi); else warp_argmax_first_halves(best, bi, gshift);
     out_d = best;
     out_pair = bi < 0 ? -1 : (bi >> 16) * nEb + (bi & 0xffff);  // flat pair index ia * nEdgesB + jb
 }

@@ -313,7 +313,6 @@ XD void sat_single(const StagedParams& P, const HullTable& T, int4 d, float* WA,
 XD void sat_dual_cubes(const StagedParams& P, const HullTable& T, int4 d, bool valid, float* W, float* Qregion, int lane) {
     const int B = P.B, maxV = P.S.maxV;
     const int half = lane >> 4, hl = lane & 15, gshift = half * 16;
-    const unsigned gmask = 0xffffu << gshift;
     float* WA = W + half * 3 * kVertWords * maxV; float* WB = WA + kVertWords * maxV; float* Lc = WB + kVertWords * maxV;
     float* Q = Qregion + half * kEdgeQueueWordsHalf;
     const int64_t world = d.w;
@@ -338,15 +337,15 @@ XD void sat_dual_cubes(const StagedParams& P, const HullTable& T, int4 d, bool v
     float da, db = 0.f, de = 0.f;
     int fa, fb = -1, ep = -1;
     PairFeature pf; pf.feature = kNone; pf.index = -1;
-    face_query_t<6, 8, 16>(planesA, 6, finvA, WB, 8, Lc, hl, da, fa, gmask);
+    face_query_t<6, 8, 16>(planesA, 6, finvA, WB, 8, Lc, hl, da, fa, gshift);
     bool open = valid && !(da >= 0.0f);  // this half's candidate still needs the next query
     if (__any_sync(0xffffffffu, open)) {
-        face_query_t<6, 8, 16>(planesB, 6, finvB, WA, 8, Lc, hl, db, fb, gmask);
+        face_query_t<6, 8, 16>(planesB, 6, finvB, WA, 8, Lc, hl, db, fb, gshift);
         open = open && !(db >= 0.0f);
         if (__any_sync(0xffffffffu, open)) {
             const int2* EA = reinterpret_cast<const int2*>(T.words + hA.edge_off);
             const int2* EB = reinterpret_cast<const int2*>(T.words + hB.edge_off);
-            edge_query_t<8, 12, 8, 12, 16>(EA, EB, 8, 12, 8, 12, WA, WB, v3(ca4.x, ca4.y, ca4.z), Q, hl, de, ep, gmask, gshift);
+            edge_query_t<8, 12, 8, 12, 16>(EA, EB, 8, 12, 8, 12, WA, WB, v3(ca4.x, ca4.y, ca4.z), Q, hl, de, ep, gshift);
             if (open && !(de >= 0.0f)) pf = choose_feature(da, fa, db, fb, de, ep);
         }
     }
