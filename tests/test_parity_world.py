@@ -218,6 +218,16 @@ def test_c4_shard_equals_slice_of_the_whole():
     assert np.array_equal(xo.rigid38(whole[8:]), xo.rigid38(part))
 
 
+def test_large_world_without_pair_table(world_path):
+    """125 bodies per world: more body pairs than the prepare stage's shared-memory pair table holds (B > 91), so the
+    broadphase takes its row-by-row path; dense lattice, so the pair capacity (4 B) is also put under pressure."""
+    if world_path == "fused":
+        pytest.skip("125 bodies per world exceed the fused kernel's shared-memory world size")
+    init, hulls, ids, joints = scenes.c4_pile(3, n_side=5, spacing=1.5)
+    _, c = _check(init, hulls, 40, 20, hull_ids=ids, joints=joints)
+    assert c["pairs_tested"] > 100_000 and c["manifolds"] > 3000
+
+
 def test_c4_full_size_properties_and_sampled_parity(world_path):
     """C4 at BASELINE size (16 384 worlds x 64 bodies, 32 joints): duplicated worlds give identical results, no NaN,
     no capacity overflow, nothing tunnels through the ground; a sample of worlds is compared with the oracle."""
