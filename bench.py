@@ -354,13 +354,13 @@ def main():
                 "share_of_step": stage_ms[1] / max(sum(stage_ms), 1e-9),
                 "step": line["roofline"],
                 "note": "dominant kernel of the staged pipeline, timed with CUDA events on the batch stream inside the library; "
-                        "FP32-issue bound (C3: 569 FADD/FMUL/FFMA of 1 274 warp-instructions per pair, DESIGN.md section 5), so the HBM fraction is small by construction",
+                        "FP32-issue bound (C3: 569 FADD/FMUL/FFMA of 1 190 warp-instructions per pair, DESIGN.md section 5), so the HBM fraction is small by construction",
             }
             if "fp32" in line["roofline"]["step"]:
                 line["roofline"]["fp32"] = line["roofline"]["step"].pop("fp32")
                 if args.workload == "c3":
                     # FP32 work of one cube-cube candidate = 17 480 thread-level flops (FADD + FMUL + 2 x FFMA, ncu SASS page
-                    # of stage_sat_cubes_kernel, profiles/r01h_stage_sat_cubes.txt / DESIGN.md section 5):
+                    # of stage_sat_cubes_kernel, profiles/r01h_stage_sat.txt / DESIGN.md section 5):
                     # the arithmetic of the reference's brute-force face + edge queries, nothing recomputed.
                     fp = line["roofline"]["fp32"]
                     fp["flops_per_pair"] = 17480.0
