@@ -253,14 +253,18 @@ def main():
     # per-stage device times of the staged multi-body pipeline (CUDA events on the batch stream around each kernel of
     # the last substep of a step call; xpbd_step_stats.stage_ms), averaged over a few extra untimed step calls
     stage_ms, cand_pairs = None, 0
+    sub_batches = int(stats.get("sub_batches", 1))
     if stats["kernel_launches"] > 1:
         acc = np.zeros(4)
+        w.set_sub_batches(1)  # each stage kernel timed ALONE: one chain of launches on the batch stream (the timed region above
+        #                       runs `sub_batches` world ranges concurrently, so there a kernel's wall time includes its neighbours)
         for _ in range(5):
             w.integrate(dt, S, 1, sync=True)
             st_ = w.stats()
             acc += np.array(st_["stage_ms"])
             cand_pairs = int(st_["candidate_pairs"])
         stage_ms = (acc / 5).tolist()
+        w.set_sub_batches(0)
     t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
     if world_size > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -312,7 +316,8 @@ def main():
             "config": {"workload": cfg["desc"], "worlds_per_gpu": n_worlds, "bodies_per_world": B, "substeps": S,
                        "dt": "1/60", "preroll_frames": cfg["preroll"], "parallelism": f"worlds sharded x{world_size}, no collective",
                        "l2": f"inputs larger than L2: {n_bodies * 152 / 1e6:.0f} MB of body state per GPU",
-                       "fma": "off (bit parity with the fp32 oracle)"},
+                       "fma": "off (bit parity with the fp32 oracle)",
+                       "sub_batches": f"{sub_batches} contiguous world ranges per GPU stepped concurrently on {sub_batches} streams (xpbd_batch_set_sub_batches, automatic)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": io_bytes, "d2h_bytes_per_step": io_bytes,
                     "what": "xpbd_batch_upload_dynamic_f32 (pinned host) + xpbd_batch_step + xpbd_batch_download_dynamic_f32, wall clock"},
             "gpu_launches": args.steps * stats["kernel_launches"],
@@ -353,7 +358,7 @@ def main():
                 "stage_ms": dict(zip(["prepare", "sat", "manifold", "solve"], stage_ms)),
                 "share_of_step": stage_ms[1] / max(sum(stage_ms), 1e-9),
                 "step": line["roofline"],
-                "note": "dominant kernel of the staged pipeline, timed with CUDA events on the batch stream inside the library; "
+                "note": "dominant kernel of the staged pipeline, timed ALONE (sub-batches = 1) with CUDA events on the batch stream inside the library; "
                         "FP32-issue bound (C3: 569 FADD/FMUL/FFMA of 1 190 warp-instructions per pair, DESIGN.md section 5), so the HBM fraction is small by construction",
             }
             if "fp32" in line["roofline"]["step"]:

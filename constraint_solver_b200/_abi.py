@@ -87,6 +87,8 @@ class StepStatsC(C.Structure):
         ("kernel_launches", C.c_int32),
         ("stage_ms", C.c_float * 4),
         ("candidate_pairs", C.c_uint64),
+        ("sub_batches", C.c_int32),
+        ("reserved", C.c_int32),
     ]
 
 
@@ -112,6 +114,7 @@ _PROTOTYPES = {
     "xpbd_batch_set_hulls": (C.c_int, [_VP, C.c_int64, C.c_int64, _VP]),
     "xpbd_batch_set_joints": (C.c_int, [_VP, C.c_int64, C.c_int64, _VP]),
     "xpbd_batch_set_stream": (C.c_int, [_VP, _VP]),
+    "xpbd_batch_set_sub_batches": (C.c_int, [_VP, C.c_int32]),
     "xpbd_batch_upload": (C.c_int, [_VP, C.c_int64, C.c_int64, _VP]),
     "xpbd_batch_download": (C.c_int, [_VP, C.c_int64, C.c_int64, _VP]),
     "xpbd_batch_upload_broadcast": (C.c_int, [_VP, _VP]),

@@ -120,6 +120,7 @@ void DeviceHulls::release() {
 int finalize_hulls(xpbd_batch* b) {
     if (!b->hulls_dirty) return XPBD_OK;
     if (b->hulls.empty()) return fail(XPBD_ERR_STATE, "no hull registered: call xpbd_batch_add_hull first");
+    b->fork_needed = true;
     int rc = b->dev_hulls.upload(b->hulls, b->stream);
     if (rc != XPBD_OK) return rc;
     b->hulls_dirty = false;

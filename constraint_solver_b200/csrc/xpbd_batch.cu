@@ -154,6 +154,7 @@ int xpbd_batch_add_hull(xpbd_batch* b, const xpbd_polytope* hull, int32_t* hull_
 
 int xpbd_batch_set_hulls(xpbd_batch* b, int64_t first_world, int64_t n_worlds, const int32_t* ids) {
     if (int rc = check_batch(b)) return rc;
+    b->fork_needed = true;
     if (int rc = check_range(b, first_world, n_worlds)) return rc;
     if (int rc = bind_device(b)) return rc;
     const int64_t B = b->desc.bodies_per_world, n = n_worlds * B;
@@ -177,6 +178,7 @@ int xpbd_batch_set_hulls(xpbd_batch* b, int64_t first_world, int64_t n_worlds, c
 
 int xpbd_batch_set_joints(xpbd_batch* b, int64_t first_world, int64_t n_worlds, const xpbd_joint* joints) {
     if (int rc = check_batch(b)) return rc;
+    b->fork_needed = true;
     if (int rc = check_range(b, first_world, n_worlds)) return rc;
     if (!joints) return fail(XPBD_ERR_INVALID, "joints is null");
     const int J = b->desc.joints_per_world;
@@ -205,6 +207,7 @@ int xpbd_batch_set_joints(xpbd_batch* b, int64_t first_world, int64_t n_worlds, 
 
 int xpbd_batch_set_stream(xpbd_batch* b, void* cuda_stream) {
     if (int rc = check_batch(b)) return rc;
+    b->fork_needed = true;
     if (int rc = bind_device(b)) return rc;
     XPBD_CUDA_TRY(cudaStreamSynchronize(b->stream));
     if (b->own_stream) cudaStreamDestroy(b->stream);
@@ -213,8 +216,17 @@ int xpbd_batch_set_stream(xpbd_batch* b, void* cuda_stream) {
     return XPBD_OK;
 }
 
+int xpbd_batch_set_sub_batches(xpbd_batch* b, int32_t count) {
+    if (int rc = check_batch(b)) return rc;
+    if (count < 0 || count > 8) return fail(XPBD_ERR_INVALID, "sub-batch count must be 0 (automatic) .. 8");
+    b->sub_batches = count;
+    b->fork_needed = true;
+    return XPBD_OK;
+}
+
 int xpbd_batch_upload(xpbd_batch* b, int64_t first_world, int64_t n_worlds, const xpbd_rigid* rigids) {
     if (int rc = check_batch(b)) return rc;
+    b->fork_needed = true;
     if (int rc = check_range(b, first_world, n_worlds)) return rc;
     if (!rigids) return fail(XPBD_ERR_INVALID, "rigids is null");
     if (int rc = bind_device(b)) return rc;
@@ -236,6 +248,7 @@ int xpbd_batch_upload(xpbd_batch* b, int64_t first_world, int64_t n_worlds, cons
 
 int xpbd_batch_download(xpbd_batch* b, int64_t first_world, int64_t n_worlds, xpbd_rigid* rigids) {
     if (int rc = check_batch(b)) return rc;
+    b->fork_needed = true;
     if (int rc = check_range(b, first_world, n_worlds)) return rc;
     if (!rigids) return fail(XPBD_ERR_INVALID, "rigids is null");
     if (int rc = bind_device(b)) return rc;
@@ -257,6 +270,7 @@ int xpbd_batch_download(xpbd_batch* b, int64_t first_world, int64_t n_worlds, xp
 
 int xpbd_batch_upload_broadcast(xpbd_batch* b, const xpbd_rigid* world_bodies) {
     if (int rc = check_batch(b)) return rc;
+    b->fork_needed = true;
     if (!world_bodies) return fail(XPBD_ERR_INVALID, "world_bodies is null");
     if (int rc = bind_device(b)) return rc;
     if (int rc = ensure_stage(b)) return rc;
@@ -281,6 +295,7 @@ static int ensure_dyn_stage(xpbd_batch* b) {
 // Asynchronous on the batch stream except for the final synchronize (the caller owns `out`).
 int xpbd_batch_download_dynamic_f32(xpbd_batch* b, int64_t first_world, int64_t n_worlds, float* out) {
     if (int rc = check_batch(b)) return rc;
+    b->fork_needed = true;
     if (int rc = check_range(b, first_world, n_worlds)) return rc;
     if (!out) return fail(XPBD_ERR_INVALID, "out is null");
     if (int rc = bind_device(b)) return rc;
@@ -296,6 +311,7 @@ int xpbd_batch_download_dynamic_f32(xpbd_batch* b, int64_t first_world, int64_t 
 
 int xpbd_batch_upload_dynamic_f32(xpbd_batch* b, int64_t first_world, int64_t n_worlds, const float* in) {
     if (int rc = check_batch(b)) return rc;
+    b->fork_needed = true;
     if (int rc = check_range(b, first_world, n_worlds)) return rc;
     if (!in) return fail(XPBD_ERR_INVALID, "in is null");
     if (int rc = bind_device(b)) return rc;
@@ -317,10 +333,12 @@ int xpbd_batch_step(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_f
     XPBD_CUDA_TRY(cudaEventRecord(b->ev_start, b->stream));
     XPBD_CUDA_TRY(cudaMemsetAsync(b->d_counters, 0, 4 * sizeof(unsigned long long), b->stream));
     b->stage_timed = false;
+    b->last.sub_batches = 1;
     const bool world_path = b->desc.body_body_contacts != 0 || b->desc.joints_per_world > 0;
     int rc = world_path ? step_world(b, (float)dt, substep_count, n_frames)
                         : step_single(b, (float)dt, substep_count, n_frames);
     if (rc != XPBD_OK) return rc;
+    if (b->last.sub_batches <= 1) b->fork_needed = true;  // this step's kernels ran on the batch stream itself
     XPBD_CUDA_TRY(cudaMemcpyAsync(b->h_counters, b->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost,
                                   b->stream));
     XPBD_CUDA_TRY(cudaEventRecord(b->ev_stop, b->stream));
@@ -345,14 +363,16 @@ int xpbd_batch_last_stats(xpbd_batch* b, xpbd_step_stats* out) {
     float ms = 0.f;
     XPBD_CUDA_TRY(cudaEventElapsedTime(&ms, b->ev_start, b->ev_stop));
     b->last.elapsed_ms = ms;
-    b->last.constraints = b->h_counters[0];
-    b->last.overflow_worlds = b->h_counters[1];
-    b->last.candidate_pairs = b->stage_timed ? b->h_counters[3] : 0;
+    unsigned long long cnt[4] = {b->h_counters[0], b->h_counters[1], b->h_counters[2], b->h_counters[3]};
+    if (b->last.sub_batches > 1) staged_add_range_counters(b, cnt);
+    b->last.constraints = cnt[0];
+    b->last.overflow_worlds = cnt[1];
+    b->last.candidate_pairs = b->stage_timed ? cnt[3] : 0;
     for (int k = 0; k < 4; ++k) {
         b->last.stage_ms[k] = 0.f;
         if (b->stage_timed) XPBD_CUDA_TRY(cudaEventElapsedTime(&b->last.stage_ms[k], b->ev_stage[k], b->ev_stage[k + 1]));
     }
-    if (b->h_counters[2]) set_error("TMA hull staging fell back to plain loads in %llu blocks", b->h_counters[2]);
+    if (cnt[2]) set_error("TMA hull staging fell back to plain loads in %llu blocks", cnt[2]);
     *out = b->last;
     return XPBD_OK;
 }

@@ -106,6 +106,13 @@ struct xpbd_batch {
     xpbd_step_stats last{};
     bool stepped = false;
     void* world_scratch = nullptr;  // owned by the multi-body path
+    int sub_batches = 0;            // xpbd_batch_set_sub_batches: 0 = automatic
+    // Set by every call that enqueues work on `stream` touching the batch's device memory (uploads, downloads, hull /
+    // joint tables, a new stream); cleared by a step call.  When the staged pipeline runs several world ranges on its
+    // internal streams, those streams wait for `stream` only if this is set — between back-to-back step calls each
+    // range just continues behind its own previous frame, so the ranges drift out of phase and kernels of different
+    // stages overlap (a barrier per frame would re-align them).
+    bool fork_needed = true;
 };
 
 namespace xpbd {
@@ -115,4 +122,6 @@ int step_world_fused(xpbd_batch* b, float frame_dt, int substeps, int n_frames);
 int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames);  // xpbd_staged.cu
 int step_world(xpbd_batch* b, float frame_dt, int substeps, int n_frames);         // picks one of the two
 void release_world_scratch(xpbd_batch* b);
+// adds the per-range counters of the last staged step call (valid once ev_stop has completed) to acc[0..3]
+void staged_add_range_counters(const xpbd_batch* b, unsigned long long* acc);
 }  // namespace xpbd

@@ -123,6 +123,11 @@ class Worlds:
     def set_stream(self, cuda_stream: int) -> None:
         _abi.check(self._lib.xpbd_batch_set_stream(self._h, C.c_void_p(cuda_stream)))
 
+    def set_sub_batches(self, count: int) -> None:
+        """World ranges stepped concurrently by the staged multi-body pipeline (0 = automatic, 1 = a single chain of
+        launches; results do not depend on it)."""
+        _abi.check(self._lib.xpbd_batch_set_sub_batches(self._h, int(count)))
+
     def upload(self, rigids: np.ndarray, first_world: int = 0) -> None:
         rigids = np.ascontiguousarray(rigids, dtype=_abi.RIGID_DTYPE).reshape(-1, self.bodies_per_world)
         _abi.check(self._lib.xpbd_batch_upload(self._h, first_world, len(rigids), _abi.ptr(rigids)))

@@ -122,6 +122,8 @@ typedef struct xpbd_step_stats {
      * call (prepare, sat, manifold, solve) and the number of candidate body pairs that substep's SAT stage processed. */
     float stage_ms[4];
     uint64_t candidate_pairs;
+    int32_t sub_batches;        /* world ranges the last step call ran concurrently (see xpbd_batch_set_sub_batches) */
+    int32_t reserved;
 } xpbd_step_stats;
 
 /* ---- library / device ---------------------------------------------------------------- */
@@ -155,6 +157,12 @@ int xpbd_batch_set_hulls(xpbd_batch* batch, int64_t first_world, int64_t n_world
 int xpbd_batch_set_joints(xpbd_batch* batch, int64_t first_world, int64_t n_worlds, const xpbd_joint* joints);
 /* Use the caller's CUDA stream (a cudaStream_t passed as void*) for every later launch/copy. */
 int xpbd_batch_set_stream(xpbd_batch* batch, void* cuda_stream);
+/* Multi-body staged pipeline: number of contiguous world ranges ("sub-batches") a step call runs concurrently, each
+ * as its own chain of launches on an internal stream forked from / joined into the batch stream.  Worlds are
+ * independent (src/world.rs:41-42), so results do not depend on it; kernels of different stages then share the SMs.
+ * 0 = automatic (one range per 2^18 bodies, at most 4), 1 = one chain of launches on the batch stream (what
+ * xpbd_step_stats.stage_ms needs to time each kernel alone), up to 8. */
+int xpbd_batch_set_sub_batches(xpbd_batch* batch, int32_t count);
 
 /* ---- state: Rigid AoS f64 <-> fp32 SoA in HBM ------------------------------------------ */
 /* rigids: n_worlds x bodies_per_world records, world-major. */

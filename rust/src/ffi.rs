@@ -92,6 +92,8 @@ pub struct xpbd_step_stats {
     pub kernel_launches: i32,
     pub stage_ms: [f32; 4],
     pub candidate_pairs: u64,
+    pub sub_batches: i32,
+    pub reserved: i32,
 }
 
 #[repr(C)]
@@ -110,6 +112,7 @@ extern "C" {
     pub fn xpbd_batch_set_hulls(batch: *mut xpbd_batch, first: i64, n: i64, ids: *const i32) -> c_int;
     pub fn xpbd_batch_set_joints(batch: *mut xpbd_batch, first: i64, n: i64, joints: *const xpbd_joint) -> c_int;
     pub fn xpbd_batch_set_stream(batch: *mut xpbd_batch, cuda_stream: *mut c_void) -> c_int;
+    pub fn xpbd_batch_set_sub_batches(batch: *mut xpbd_batch, count: i32) -> c_int;
     pub fn xpbd_batch_upload(batch: *mut xpbd_batch, first: i64, n: i64, rigids: *const xpbd_rigid) -> c_int;
     pub fn xpbd_batch_download(batch: *mut xpbd_batch, first: i64, n: i64, rigids: *mut xpbd_rigid) -> c_int;
     pub fn xpbd_batch_upload_broadcast(batch: *mut xpbd_batch, world_bodies: *const xpbd_rigid) -> c_int;

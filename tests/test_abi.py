@@ -32,7 +32,7 @@ def test_every_declared_symbol_is_exported_and_bound():
 def test_record_layouts_match_header():
     assert _abi.RIGID_DTYPE.itemsize == 304 and _abi.FRAME_DTYPE.itemsize == 56
     assert _abi.CONSTRAINT_DTYPE.itemsize == 64 and _abi.JOINT_DTYPE.itemsize == 64
-    assert C.sizeof(_abi.StepStatsC) == 56 and C.sizeof(_abi.BatchDescC) == 48
+    assert C.sizeof(_abi.StepStatsC) == 64 and C.sizeof(_abi.BatchDescC) == 48
 
 
 def test_version_string():

@@ -24,10 +24,12 @@ def world_path(request, monkeypatch):
 CUBE = cs.Polytope.new_cube()
 
 
-def _run_gpu(init, hulls, frames, substeps, hull_ids=None, joints=None, body_body=True, per_frame=False, **kw):
+def _run_gpu(init, hulls, frames, substeps, hull_ids=None, joints=None, body_body=True, per_frame=False, sub_batches=0, **kw):
     n, B = init.shape
     J = 0 if joints is None else joints.shape[1]
     with cs.Worlds(n, B, joints_per_world=J, body_body_contacts=body_body, **kw) as w:
+        if sub_batches:
+            w.set_sub_batches(sub_batches)
         for h in hulls:
             w.add_hull(h)
         if hull_ids is not None:
@@ -45,6 +47,8 @@ def _run_gpu(init, hulls, frames, substeps, hull_ids=None, joints=None, body_bod
             cons = w.stats()["constraints"]
         st = w.stats()
         assert st["overflow_worlds"] == 0
+        if sub_batches and st["kernel_launches"] > 1:  # the staged pipeline ran: it must have used that many world ranges
+            assert st["sub_batches"] == min(sub_batches, n)
         return w.download(), cons
 
 
@@ -56,8 +60,8 @@ def _run_cpu(init, hulls, frames, substeps, hull_ids=None, joints=None, body_bod
     return r, c
 
 
-def _check(init, hulls, frames, substeps, **kw):
-    gpu, gcons = _run_gpu(init, hulls, frames, substeps, **kw)
+def _check(init, hulls, frames, substeps, sub_batches=0, **kw):
+    gpu, gcons = _run_gpu(init, hulls, frames, substeps, sub_batches=sub_batches, **kw)
     cpu, c = _run_cpu(init, hulls, frames, substeps, **kw)
     pos, rot, exact = parity.compare(gpu, cpu)
     assert pos <= parity.POS_TOL and rot <= parity.ROT_TOL, (pos, rot)
@@ -178,6 +182,62 @@ def test_stack_with_attachment_joints_and_contacts():
 def test_ragged_world_count_and_friction_compliance_params():
     init = scenes.c3_stack(13, n_cubes=3)  # not a multiple of the worlds-per-block
     _check(init, [CUBE], 30, 10, friction=0.5, compliance=1e-5)
+
+
+@pytest.mark.parametrize("k", [2, 3, 8])
+def test_sub_batches_do_not_change_results(world_path, k):
+    """xpbd_batch_set_sub_batches: the staged pipeline steps k contiguous world ranges concurrently on k streams (pointer
+    offsets into every per-world / per-body array, hull ids and joints included).  Ragged world counts, more ranges
+    than some ranges have worlds to fill a block, joints + mixed hulls; bit-identical to the oracle."""
+    if world_path == "fused":
+        pytest.skip("sub-batches are a schedule of the staged pipeline")
+    init, hulls, ids, joints = scenes.c4_pile(13)
+    _, c = _check(init, hulls, 30, 20, hull_ids=ids, joints=joints, sub_batches=k)
+    assert c["manifolds"] > 0
+    init = scenes.c3_stack(37)
+    _check(init, [CUBE], 30, 20, sub_batches=k)
+    _check(scenes.c3_stack(5, n_cubes=3), [CUBE], 10, 10, sub_batches=8)  # more ranges than worlds
+
+
+def test_sub_batches_back_to_back_step_calls(world_path):
+    """Between back-to-back step calls the world ranges do not wait for each other (no per-frame barrier); an
+    asynchronous upload in between makes them wait for the batch stream again.  Same bits as the oracle either way."""
+    if world_path == "fused":
+        pytest.skip("sub-batches are a schedule of the staged pipeline")
+    n = 257
+    init = scenes.c3_stack(n)
+    cpu, _ = _run_cpu(init, [CUBE], 12, 20)
+    with cs.Worlds(n, 10, body_body_contacts=True) as w:
+        w.add_hull(CUBE)
+        w.set_sub_batches(4)
+        w.upload(init)
+        for _ in range(6):
+            w.integrate(DT, 20, 1, sync=False)
+        snap = w.download_dynamic()          # joins, reads
+        w.upload_dynamic(snap)               # asynchronous on the batch stream: the ranges must wait for it
+        for _ in range(6):
+            w.integrate(DT, 20, 1, sync=False)
+        got = w.download()
+        assert w.stats()["sub_batches"] == 4
+    assert np.array_equal(xo.rigid38(got), cpu.astype(np.float64))
+
+
+def test_sub_batches_stats_sum_over_ranges(world_path):
+    """constraints / candidate_pairs of xpbd_step_stats are totals over all world ranges."""
+    if world_path == "fused":
+        pytest.skip("sub-batches are a schedule of the staged pipeline")
+    init = scenes.c3_stack(64)
+    res = []
+    for k in (1, 4):
+        with cs.Worlds(64, 10, body_body_contacts=True) as w:
+            w.add_hull(CUBE)
+            w.set_sub_batches(k)
+            w.upload(init)
+            w.integrate(DT, 20, 15)
+            st = w.stats()
+            res.append((st["constraints"], st["candidate_pairs"], st["overflow_worlds"]))
+            assert st["sub_batches"] == k and st["kernel_launches"] == k * 4 * 20 * 15
+    assert res[0] == res[1] and res[0][1] > 0
 
 
 def test_c3_full_size_properties_and_sampled_parity():
