@@ -262,6 +262,193 @@ XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int 
     out_d = best;
     out_pair = bi < 0 ? -1 : (bi >> 16) * nEb + (bi & 0xffff);  // flat pair index ia * nEdgesB + jb
 }
+// ---- culled edge query ------------------------------------------------------------------------------------------------
+// What the step needs from the edge query is only (a) whether some edge axis separates the hulls (distance >= 0) and
+// (b) whether the best edge axis beats the faces in choose_feature (distance > kRelEdge * face_max + kAbsTol) — and, only
+// then, which pair it is.  So with T = min(0, kRelEdge * face_max + kAbsTol) any edge pair whose distance is PROVABLY
+// below T can be dropped without changing the outcome: if the true maximum is >= T its pair is never dropped and
+// (distance, pair) come out bit-identical; if it is < T both tests fail for the true and for the culled maximum alike.
+//
+// The proof per pair is a witness: for ANY vertex w of B,
+//     distance = min_v dot(axis, B_v) - displacement  <=  dot(axis, w) - displacement  ~=  dot(axis, w - foot),
+// and the sign / size of dot(axis, w - foot) can be read off the UNNORMALISED cross product c = edge_a x edge_b:
+//     dot(axis, w - foot) = s * dot(c, w - foot) / |c|,   s = sign of dot(c, foot - centroid_A)   (the reference's flip).
+// Stage 1 (all pairs; no sqrt, no reciprocal, no support scan): cull when s * dot(c, w - foot) < -(|T| + M) |c|, compared
+// in squared form, where M bounds every rounding difference between this estimate and the fp32 value the reference
+// arithmetic produces (about 4e-6 * R for coordinates up to R; M = 4e-5 * (1 + R), ten times that).  A pair whose flip sign
+// is not clear-cut (|dot(c, foot - centroid_A)| <= M |c|) is kept.  A pair with |c|^2 == 0 or NaN (parallel edges; NaN
+// vertices) has a NaN distance in the reference arithmetic, which can never win: culled.
+// Stage 2 (survivors, through the warp-private queue): the reference's arithmetic for that pair, unchanged — axis,
+// flip, support scan of A, plane displacement, support scan of B, "first strict maximum" tie rule.
+// Two witnesses are used (witness_vertices: B's deepest vertex below A's best face and a second deep vertex far from it);
+// any vertices would be valid, these sit in the contact region, where they cull most.
+#ifdef XPBD_CULL_STATS
+__device__ unsigned long long g_cull_stats[3];  // edge queries, pairs kept by stage 1, pairs seen (debug builds: scripts/cull_stats.sh)
+#endif
+struct EdgeCull {
+    float T;    // min(0, kRelEdge * face_max + kAbsTol)
+    float M;    // rounding margin, 4e-5 * (1 + largest |coordinate| of the two hulls' world vertices)
+    V3 w1, w2;  // witnesses: two world-space vertices of B (the smaller of the two bounds is used)
+};
+XD EdgeCull make_edge_cull(float da, float db, float max_abs_coord, V3 witness1, V3 witness2) {
+    EdgeCull c;
+    const float face_max = da > db ? da : db;
+    c.T = fminf(0.0f, fadd(fmul(kRelEdge, face_max), kAbsTol));
+    c.M = 4e-5f * (1.0f + max_abs_coord);
+    c.w1 = witness1;
+    c.w2 = witness2;
+    return c;
+}
+// Index of (approximately) the vertex with the smallest dot(n, L_v): the low bits of the ordered key carry the index.
+// Only feeds the cull's witness, so neither ties nor the few mantissa bits given up matter.
+template <int LG>
+XD int min_key_vertex(uint32_t key, int nB, int gshift) {
+    if (LG == 32) {
+        key = __reduce_min_sync(0xffffffffu, key);
+    } else {
+        const bool hi = gshift != 0;
+        const uint32_t lo_min = __reduce_min_sync(0xffffffffu, hi ? 0xffffffffu : key);
+        const uint32_t hi_min = __reduce_min_sync(0xffffffffu, hi ? key : 0xffffffffu);
+        key = hi ? hi_min : lo_min;
+    }
+    const int v = (int)(key & 63u);
+    return v < nB ? v : 0;
+}
+XD uint32_t ordered_key_with_index(float d, int v) {
+    const uint32_t u = (uint32_t)__float_as_int(d);
+    return (((u & 0x80000000u) ? ~u : (u | 0x80000000u)) & ~63u) | (uint32_t)v;
+}
+// Two witnesses for the cull, as vertex indices of B: the deepest vertex below the plane (L = B's vertices in the
+// plane's space), and a second one that is deep too but far from the first (depth minus half the distance to the first):
+// two points of the contact region that are not collinear with most edge feet, so that only axes close to the contact
+// normal survive both bounds.  Heuristics only — any two vertices are valid witnesses.
+template <int LG>
+XD int2 witness_vertices(float4 plane, const float* L, int nB, int lane, int gshift) {
+    const V3 n = v3(plane.x, plane.y, plane.z);
+    uint32_t key = 0xffffffffu;
+    for (int v = lane; v < nB; v += LG) { const uint32_t k = ordered_key_with_index(dot(n, ld3(L, v)), v); key = k < key ? k : key; }
+    const int v1 = min_key_vertex<LG>(key, nB, gshift);
+    const V3 p1 = ld3(L, v1);
+    key = 0xffffffffu;
+    for (int v = lane; v < nB; v += LG) {
+        const V3 p = ld3(L, v);
+        const uint32_t k = ordered_key_with_index(dot(n, p) - 0.5f * sqrtf(magnitude2(p - p1)), v);
+        key = k < key ? k : key;
+    }
+    return make_int2(v1, min_key_vertex<LG>(key, nB, gshift));
+}
+
+template <int NVA, int NEA, int NVB, int NEB, int LG = 32>
+XD void edge_query_culled_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int nB_rt, int nEb_rt, const float* WA,
+                            const float* WB, V3 CA, float* Q, int lane, EdgeCull cull, float& out_d, int& out_pair,
+                            int gshift = 0) {
+    float best = -FLT_MAX;
+    int bi = -1;
+    const int nA = NVA ? NVA : nA_rt, nB = NVB ? NVB : nB_rt;
+    const int nEb = NEB ? NEB : nEb_rt, nPairs = (NEA ? NEA : nEa_rt) * nEb;
+    int* Qi = reinterpret_cast<int*>(Q);  // survivor queue: kQueueCap entries (ia << 16 | jb) in the words ahead of the edge table
+    constexpr int kQueueCap = 4 * 2 * LG;
+    constexpr bool kTable = NEA > 0 && NEB > 0 && 2 * NEA + NEB <= kEdgeTableMax;
+    float* EV = Q + 4 * 2 * LG;  // [0, NEA) edge_a | [NEA, 2 NEA) foot | [2 NEA, 2 NEA + NEB) edge_b
+    if (kTable) {
+        for (int t = lane; t < NEA + NEB; t += LG) {
+            if (t < NEA) {
+                const int2 ea = EA[t];
+                const V3 foot = ld3(WA, ea.x);
+                st3(EV, t, ld3(WA, ea.y) - foot);
+                st3(EV, NEA + t, foot);
+            } else {
+                const int2 eb = EB[t - NEA];
+                st3(EV, NEA + t, ld3(WB, eb.y) - ld3(WB, eb.x));
+            }
+        }
+        __syncwarp();
+    }
+    auto load_pair = [&](int ia, int jb, V3& foot, V3& edge_a, V3& edge_b) {
+        if (kTable) {
+            foot = ld3(EV, NEA + ia); edge_a = ld3(EV, ia); edge_b = ld3(EV, 2 * NEA + jb);
+        } else {
+            const int2 ea = EA[ia], eb = EB[jb];
+            foot = ld3(WA, ea.x);
+            edge_a = ld3(WA, ea.y) - foot;
+            edge_b = ld3(WB, eb.y) - ld3(WB, eb.x);
+        }
+    };
+    // stage 2: the reference's arithmetic for one surviving pair (src/collision.rs:166-193)
+    auto exact_pair = [&](int e) {
+        V3 foot, edge_a, edge_b;
+        load_pair(e >> 16, e & 0xffff, foot, edge_a, edge_b);
+        V3 axis = normalize(cross(edge_a, edge_b));
+        if (dot(axis, foot - CA) < 0.0f) axis = -axis;
+        const float sa = NVA ? scan_dots_t<NVA, true>(WA, nA, axis) : scan_dots<true>(WA, nA, axis);
+        if (sa > dot(foot, axis)) return;  // another point of `a` is further in the direction to `b`
+        const float disp = plane_displacement(foot, axis);
+        const float sb = NVB ? scan_dots_t<NVB, false>(WB, nB, axis) : scan_dots<false>(WB, nB, axis);
+        const float distance = fsub(sb, disp);
+        if (distance > best || (distance == best && e < bi)) { best = distance; bi = e; }
+    };
+    const float tm = fabsf(cull.T) + cull.M;
+    const float K = tm * tm, Kf = cull.M * cull.M;
+    auto dcA_of = [&](V3 c) { return dot(c, CA); };
+    int qn = 0;  // uniform across the lane group
+#ifdef XPBD_CULL_STATS
+    int n_kept = 0;
+#endif
+    const int step_a = LG / nEb, step_b = LG - step_a * nEb;  // advancing the flat pair index by LG
+    const unsigned below_me = (1u << lane) - 1u;
+    int ia = lane / nEb, jb = lane - ia * nEb;
+#pragma unroll 1
+    for (int e0 = 0; e0 < nPairs; e0 += LG) {
+        const int e = e0 + lane;
+        bool keep = false;
+        if (e0 + LG <= nPairs || e < nPairs) {
+            V3 foot, edge_a, edge_b;
+            load_pair(ia, jb, foot, edge_a, edge_b);
+            const V3 c = cross(edge_a, edge_b);
+            const float c2 = dot(c, c);
+            const float df = dot(c, foot);
+            const float f = df - dcA_of(c);
+            const float u1 = dot(c, cull.w1) - df, u2 = dot(c, cull.w2) - df;
+            const float us = f < 0.0f ? -fmaxf(u1, u2) : fminf(u1, u2);  // the smaller of the two bounds, flipped like the axis
+            // (c2 > 1e-24: below that |c|^2 loses precision and the normalised axis is no longer unit length — left to stage 2)
+            const bool below = us < 0.0f && fmul(us, us) > fmul(K, c2) && fmul(f, f) > fmul(Kf, c2) && c2 > 1e-24f;
+            keep = !below && c2 > 0.0f;
+        }
+        const unsigned m = LG == 32 ? __ballot_sync(0xffffffffu, keep) : ((__ballot_sync(0xffffffffu, keep) >> gshift) & ((1u << (LG & 31)) - 1u));
+        if (keep) Qi[qn + __popc(m & below_me)] = (ia << 16) | jb;
+        ia += step_a; jb += step_b;
+        if (jb >= nEb) { jb -= nEb; ++ia; }
+        qn += __popc(m);
+#ifdef XPBD_CULL_STATS
+        n_kept += __popc(m);
+#endif
+        __syncwarp();
+        // Survivors are few, so they are left in the queue until the scan is over and then processed LG at a time (full
+        // lane groups; two halves in lockstep stay in step) — only a queue about to overflow is drained early.
+        const bool drain = LG == 32 ? qn > kQueueCap - LG : __any_sync(0xffffffffu, qn > kQueueCap - LG);
+        if (drain) {
+            const int take = qn < LG ? qn : LG;
+            qn -= take;
+            if (lane < take) exact_pair(Qi[qn + lane]);
+            __syncwarp();
+        }
+    }
+    for (;;) {
+        const bool more = LG == 32 ? qn > 0 : __any_sync(0xffffffffu, qn > 0);
+        if (!more) break;
+        const int take = qn < LG ? qn : LG;
+        qn -= take;
+        if (lane < take) exact_pair(Qi[qn + lane]);
+        __syncwarp();
+    }
+#ifdef XPBD_CULL_STATS
+    if (lane == 0) { atomicAdd(&g_cull_stats[0], 1ull); atomicAdd(&g_cull_stats[1], (unsigned long long)n_kept); atomicAdd(&g_cull_stats[2], (unsigned long long)nPairs); }
+#endif
+    if (LG == 32) warp_argmax_first(best, bi); else warp_argmax_first_halves(best, bi, gshift);
+    out_d = best;
+    out_pair = bi < 0 ? -1 : (bi >> 16) * nEb + (bi & 0xffff);  // flat pair index ia * nEdgesB + jb
+}
+
 XD void edge_query(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const float* WA, const float* WB, V3 CA,
                    float* Q, int lane, float& out_d, int& out_pair) {
     const int2* EA = reinterpret_cast<const int2*>(T.words + hA.edge_off);

@@ -270,6 +270,14 @@ static_assert(2 * kEdgeQueueWordsHalf >= kEdgeQueueWords, "queue region must hol
 XD bool is_cube_shape(const HullDesc& h) { return h.n_verts == 8 && h.n_edges == 12 && h.n_faces == 6; }
 
 // One candidate on the whole warp (any hull sizes).
+// largest |x|, |y|, |z| of a vertex as an unsigned key (bit pattern of a non-negative float; NaN sorts above everything,
+// which switches the cull off)
+XD uint32_t abs_coord_key(float4 v) {
+    const uint32_t a = (uint32_t)__float_as_int(fabsf(v.x)), b = (uint32_t)__float_as_int(fabsf(v.y)), c = (uint32_t)__float_as_int(fabsf(v.z));
+    return max(a, max(b, c));
+}
+
+template <bool kCull>
 XD void sat_single(const StagedParams& P, const HullTable& T, int4 d, float* WA, float* WB, float* Lc, float* Q, int lane) {
     const int B = P.B, maxV = P.S.maxV;
     const int64_t world = d.w;
@@ -277,8 +285,9 @@ XD void sat_single(const StagedParams& P, const HullTable& T, int4 d, float* WA,
     const HullDesc& hA = T.desc(d.z & 0xffff);
     const HullDesc& hB = T.desc(d.z >> 16);
     __syncwarp();
-    for (int v = lane; v < hA.n_verts; v += 32) reinterpret_cast<float4*>(WA)[v] = P.S.verts[gi * maxV + v];
-    for (int v = lane; v < hB.n_verts; v += 32) reinterpret_cast<float4*>(WB)[v] = P.S.verts[gj * maxV + v];
+    uint32_t rkey = 0;
+    for (int v = lane; v < hA.n_verts; v += 32) { const float4 x = P.S.verts[gi * maxV + v]; reinterpret_cast<float4*>(WA)[v] = x; if (kCull) rkey = max(rkey, abs_coord_key(x)); }
+    for (int v = lane; v < hB.n_verts; v += 32) { const float4 x = P.S.verts[gj * maxV + v]; reinterpret_cast<float4*>(WB)[v] = x; if (kCull) rkey = max(rkey, abs_coord_key(x)); }
     const float4 ra = P.bodies.dynC[gi], rb = P.bodies.dynC[gj];
     const float4 fa4 = P.S.finvp[gi], fb4 = P.S.finvp[gj], ca4 = P.S.cen[gi];
     Fr finvA, finvB;
@@ -294,10 +303,18 @@ XD void sat_single(const StagedParams& P, const HullTable& T, int4 d, float* WA,
     const float4* planesB = reinterpret_cast<const float4*>(T.words + hB.plane_off);
     face_query_t<0, 0>(planesA, hA.n_faces, finvA, WB, hB.n_verts, Lc, lane, da, fa);
     if (!(da >= 0.0f)) {
+        int2 wi = make_int2(0, 0);  // the cull's witnesses: deep vertices of B below A's best face (Lc still holds B in A's space)
+        if (kCull) wi = witness_vertices<32>(planesA[fa < 0 ? 0 : fa], Lc, hB.n_verts, lane, 0);
+        __syncwarp();
         face_query_t<0, 0>(planesB, hB.n_faces, finvB, WA, hA.n_verts, Lc, lane, db, fb);
         if (!(db >= 0.0f)) {
             const int2* EA = reinterpret_cast<const int2*>(T.words + hA.edge_off);
             const int2* EB = reinterpret_cast<const int2*>(T.words + hB.edge_off);
+            if (kCull) {
+                const float R = __int_as_float((int)__reduce_max_sync(0xffffffffu, rkey));
+                edge_query_culled_t<0, 0, 0, 0>(EA, EB, hA.n_verts, hA.n_edges, hB.n_verts, hB.n_edges, WA, WB, v3(ca4.x, ca4.y, ca4.z), Q,
+                                                lane, make_edge_cull(da, db, R, ld3(WB, wi.x), ld3(WB, wi.y)), de, ep);
+            } else
             edge_query_t<0, 0, 0, 0>(EA, EB, hA.n_verts, hA.n_edges, hB.n_verts, hB.n_edges, WA, WB, v3(ca4.x, ca4.y, ca4.z), Q,
                                      lane, de, ep);
             if (!(de >= 0.0f)) pf = choose_feature(da, fa, db, fb, de, ep);
@@ -311,6 +328,7 @@ XD void sat_single(const StagedParams& P, const HullTable& T, int4 d, float* WA,
 // per-candidate setup (descriptor, vertices, frames, edge table) is issued once for both.  Each half runs exactly
 // the single-candidate arithmetic on its own scratch; the queries are entered by both halves together (a half whose
 // candidate is already separated idles through them) so that the warp never serialises the two halves.
+template <bool kCull>
 XD void sat_dual_cubes(const StagedParams& P, const HullTable& T, int4 d, bool valid, float* W, float* Qregion, int lane) {
     const int B = P.B, maxV = P.S.maxV;
     const int half = lane >> 4, hl = lane & 15, gshift = half * 16;
@@ -323,9 +341,12 @@ XD void sat_dual_cubes(const StagedParams& P, const HullTable& T, int4 d, bool v
     __syncwarp();
     float4 ra, rb, fa4, fb4, ca4;
     ra = rb = fa4 = fb4 = ca4 = make_float4(0.f, 0.f, 0.f, 1.f);
+    uint32_t rkey = 0;
     if (valid) {  // an odd work list leaves the last warp's second half without a candidate: it idles through
-        if (hl < 8) reinterpret_cast<float4*>(WA)[hl] = P.S.verts[gi * maxV + hl];
-        else reinterpret_cast<float4*>(WB)[hl - 8] = P.S.verts[gj * maxV + hl - 8];
+        const float4 x = hl < 8 ? P.S.verts[gi * maxV + hl] : P.S.verts[gj * maxV + hl - 8];
+        if (hl < 8) reinterpret_cast<float4*>(WA)[hl] = x;
+        else reinterpret_cast<float4*>(WB)[hl - 8] = x;
+        if (kCull) rkey = abs_coord_key(x);
         ra = P.bodies.dynC[gi]; rb = P.bodies.dynC[gj];
         fa4 = P.S.finvp[gi]; fb4 = P.S.finvp[gj]; ca4 = P.S.cen[gi];
     }
@@ -341,11 +362,21 @@ XD void sat_dual_cubes(const StagedParams& P, const HullTable& T, int4 d, bool v
     face_query_t<6, 8, 16>(planesA, 6, finvA, WB, 8, Lc, hl, da, fa, gshift);
     bool open = valid && !(da >= 0.0f);  // this half's candidate still needs the next query
     if (__any_sync(0xffffffffu, open)) {
+        int2 wi = make_int2(0, 0);  // the cull's witnesses: deep vertices of B below A's best face (Lc still holds B in A's space)
+        if (kCull) wi = witness_vertices<16>(planesA[fa < 0 ? 0 : fa], Lc, 8, hl, gshift);
+        __syncwarp();
         face_query_t<6, 8, 16>(planesB, 6, finvB, WA, 8, Lc, hl, db, fb, gshift);
         open = open && !(db >= 0.0f);
         if (__any_sync(0xffffffffu, open)) {
             const int2* EA = reinterpret_cast<const int2*>(T.words + hA.edge_off);
             const int2* EB = reinterpret_cast<const int2*>(T.words + hB.edge_off);
+            if (kCull) {
+                const bool hi = gshift != 0;
+                const uint32_t r_lo = __reduce_max_sync(0xffffffffu, hi ? 0u : rkey), r_hi = __reduce_max_sync(0xffffffffu, hi ? rkey : 0u);
+                const float R = __int_as_float((int)(hi ? r_hi : r_lo));
+                edge_query_culled_t<8, 12, 8, 12, 16>(EA, EB, 8, 12, 8, 12, WA, WB, v3(ca4.x, ca4.y, ca4.z), Q, hl,
+                                                      make_edge_cull(da, db, R, ld3(WB, wi.x), ld3(WB, wi.y)), de, ep, gshift);
+            } else
             edge_query_t<8, 12, 8, 12, 16>(EA, EB, 8, 12, 8, 12, WA, WB, v3(ca4.x, ca4.y, ca4.z), Q, hl, de, ep, gshift);
             if (open && !(de >= 0.0f)) pf = choose_feature(da, fa, db, fb, de, ep);
         }
@@ -353,6 +384,7 @@ XD void sat_dual_cubes(const StagedParams& P, const HullTable& T, int4 d, bool v
     if (hl == 0 && valid) { P.S.pairs[d.x].y = pf.feature; P.S.pairs[d.x].z = pf.index; }
 }
 
+template <bool kCull>
 __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_kernel(StagedParams P) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ __align__(8) uint64_t bar;
@@ -364,10 +396,11 @@ __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_kernel(Sta
     float* Qregion = W + 6 * kVertWords * maxV;
     const unsigned count = *P.S.work_count;
     for (unsigned it = blockIdx.x * nwarps + warp; it < count; it += gridDim.x * nwarps)
-        sat_single(P, T, P.S.worklist[it], W, W + kVertWords * maxV, W + 2 * kVertWords * maxV, Qregion, lane);
+        sat_single<kCull>(P, T, P.S.worklist[it], W, W + kVertWords * maxV, W + 2 * kVertWords * maxV, Qregion, lane);
 }
 
 // Batches in which every registered hull is cube-shaped (8 vertices, 12 edges, 6 quads): two candidates per warp.
+template <bool kCull>
 __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_cubes_kernel(StagedParams P) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ __align__(8) uint64_t bar;
@@ -383,7 +416,7 @@ __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_cubes_kern
         const bool valid = mine < count;
         int4 d = make_int4(0, 0, 0, 0);
         if (valid) d = P.S.worklist[mine];  // slot, i | j << 16, hull_i | hull_j << 16, world
-        sat_dual_cubes(P, T, d, valid, W, Qregion, lane);
+        sat_dual_cubes<kCull>(P, T, d, valid, W, Qregion, lane);
     }
 }
 
@@ -766,7 +799,10 @@ static int ensure_staged(xpbd_batch* b, StagedState*& out) {
     if (st->smem_prepare > (size_t)smem_max || st->smem_sat > (size_t)smem_max || st->smem_manifold > (size_t)smem_max)
         return fail(XPBD_ERR_CAPACITY, "hull table / world too large for shared memory (%zu, %zu bytes)", st->smem_prepare, st->smem_sat);
     XPBD_CUDA_TRY(cudaFuncSetAttribute(st->prepare_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_prepare));
-    st->sat_fn = stage_sat_kernel;
+    // XPBD_SAT_CULL=0: the edge query without the witness cull (every edge pair through the reference's arithmetic) — A/B runs
+    bool cull = true;
+    if (const char* e = std::getenv("XPBD_SAT_CULL")) cull = e[0] != '0';
+    st->sat_fn = cull ? stage_sat_kernel<true> : stage_sat_kernel<false>;
     {
         bool all_cubes = !b->hulls.empty();
         for (const HostHull& h : b->hulls) {
@@ -775,7 +811,7 @@ static int ensure_staged(xpbd_batch* b, StagedState*& out) {
             all_cubes = all_cubes && h.vertices.size() == 8 * 3 && h.edges.size() == 12 * 2 && quads;
         }
         const char* e = std::getenv("XPBD_SAT_DUAL");
-        if (all_cubes && !(e && e[0] == '0')) st->sat_fn = stage_sat_cubes_kernel;
+        if (all_cubes && !(e && e[0] == '0')) st->sat_fn = cull ? stage_sat_cubes_kernel<true> : stage_sat_cubes_kernel<false>;
     }
     XPBD_CUDA_TRY(cudaFuncSetAttribute(st->sat_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_sat));
     st->manifold_fn = st->clip_cap == 8 ? stage_manifold_kernel<8> : stage_manifold_kernel<kMaxClip>;
@@ -821,6 +857,13 @@ static int ensure_sub_streams(xpbd_batch* b, StagedState* st, int n_sub) {
     }
     return XPBD_OK;
 }
+
+#ifdef XPBD_CULL_STATS
+extern "C" void xpbd_debug_cull_stats(unsigned long long out[3]) {  // debug builds only
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_cull_stats, 3 * sizeof(unsigned long long));
+}
+#endif
 
 void staged_add_range_counters(const xpbd_batch* b, unsigned long long* acc) {
     const StagedState* st = static_cast<const StagedState*>(b->world_scratch);
