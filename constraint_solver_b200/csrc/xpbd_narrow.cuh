@@ -301,6 +301,13 @@ XD EdgeCull make_edge_cull(float da, float db, float max_abs_coord, V3 witness1,
 }
 // Index of (approximately) the vertex with the smallest dot(n, L_v): the low bits of the ordered key carry the index.
 // Only feeds the cull's witness, so neither ties nor the few mantissa bits given up matter.
+// largest |x|, |y|, |z| of a vertex as an unsigned key (bit pattern of a non-negative float; NaN sorts above everything,
+// which switches the cull off)
+XD uint32_t abs_coord_key(float4 v) {
+    const uint32_t a = (uint32_t)__float_as_int(fabsf(v.x)), b = (uint32_t)__float_as_int(fabsf(v.y)), c = (uint32_t)__float_as_int(fabsf(v.z));
+    return max(a, max(b, c));
+}
+
 template <int LG>
 XD int min_key_vertex(uint32_t key, int nB, int gshift) {
     if (LG == 32) {

@@ -184,8 +184,21 @@ __global__ void __launch_bounds__(32) pair_query_kernel(const double* fa, const 
     int feature = kNone;
     face_query(T, hA, frame_inverse(FA), s.WB, hB.n_verts, s.L, lane, da, fA);
     bool hit = !(da >= 0.0f);
+    // the step's edge query: witness cull + the reference arithmetic on the survivors (same outcome as mode 1's full scan)
+    int2 wi = make_int2(0, 0);
+    if (hit) wi = witness_vertices<32>(reinterpret_cast<const float4*>(T.words + hA.plane_off)[fA < 0 ? 0 : fA], s.L, hB.n_verts, lane, 0);
+    __syncwarp();
     if (hit) { face_query(T, hB, frame_inverse(FB), s.WA, hA.n_verts, s.L, lane, db, fB); hit = !(db >= 0.0f); }
-    if (hit) { edge_query(T, hA, hB, s.WA, s.WB, CA, s.Q, lane, de, ep); hit = !(de >= 0.0f); }
+    if (hit) {
+        uint32_t rkey = 0;
+        for (int v = lane; v < hA.n_verts; v += 32) rkey = max(rkey, abs_coord_key(reinterpret_cast<const float4*>(s.WA)[v]));
+        for (int v = lane; v < hB.n_verts; v += 32) rkey = max(rkey, abs_coord_key(reinterpret_cast<const float4*>(s.WB)[v]));
+        const float R = __int_as_float((int)__reduce_max_sync(0xffffffffu, rkey));
+        edge_query_culled_t<0, 0, 0, 0>(reinterpret_cast<const int2*>(T.words + hA.edge_off), reinterpret_cast<const int2*>(T.words + hB.edge_off),
+                                        hA.n_verts, hA.n_edges, hB.n_verts, hB.n_edges, s.WA, s.WB, CA, s.Q, lane,
+                                        make_edge_cull(da, db, R, ld3(s.WB, wi.x), ld3(s.WB, wi.y)), de, ep);
+        hit = !(de >= 0.0f);
+    }
     if (lane == 0) {
         Manifold m; m.count = 0;
         int incident = 0;

@@ -270,13 +270,6 @@ static_assert(2 * kEdgeQueueWordsHalf >= kEdgeQueueWords, "queue region must hol
 XD bool is_cube_shape(const HullDesc& h) { return h.n_verts == 8 && h.n_edges == 12 && h.n_faces == 6; }
 
 // One candidate on the whole warp (any hull sizes).
-// largest |x|, |y|, |z| of a vertex as an unsigned key (bit pattern of a non-negative float; NaN sorts above everything,
-// which switches the cull off)
-XD uint32_t abs_coord_key(float4 v) {
-    const uint32_t a = (uint32_t)__float_as_int(fabsf(v.x)), b = (uint32_t)__float_as_int(fabsf(v.y)), c = (uint32_t)__float_as_int(fabsf(v.z));
-    return max(a, max(b, c));
-}
-
 template <bool kCull>
 XD void sat_single(const StagedParams& P, const HullTable& T, int4 d, float* WA, float* WB, float* Lc, float* Q, int lane) {
     const int B = P.B, maxV = P.S.maxV;

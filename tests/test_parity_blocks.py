@@ -133,8 +133,12 @@ def test_face_and_edge_queries(a, b):
         assert np.float32(edist[i]) == d and tuple(edges[i]) == e, (i, edist[i], d, edges[i], e)
 
 
+@pytest.mark.parametrize("offset", [(0.0, 0.0, 0.0), (511.3, -297.1, 88.7)], ids=["origin", "far"])
 @pytest.mark.parametrize("a,b", PAIRS)
-def test_sat_manifold(a, b):
+def test_sat_manifold(a, b, offset):
+    """The finished sat through the STEP's edge query (witness cull + reference arithmetic on the survivors): same feature,
+    same contacts as the oracle's full scan, near the origin and far from it (the cull's rounding margin scales with
+    the coordinates)."""
     (_, pa), (_, pb) = HULLS[a], HULLS[b]
     n = 600
     fa, fb = _frames(n, 31, spread=0.7), _frames(n, 32, spread=0.7)
@@ -144,6 +148,7 @@ def test_sat_manifold(a, b):
     small = scenes.random_unit_quaternions(rng, k); small[:, :3] *= 0.02; small /= np.linalg.norm(small, axis=1)[:, None]
     fa["rotation"][:k] = (0, 0, 0, 1); fa["position"][:k] = 0
     fb["rotation"][:k] = small; fb["position"][:k] = np.stack([rng.uniform(-0.3, 0.3, k), rng.uniform(-0.3, 0.3, k), rng.uniform(0.9, 1.02, k)], axis=1)
+    fa["position"] += np.array(offset); fb["position"] += np.array(offset)
     cons = np.zeros((n, 4), dtype=_abi.CONSTRAINT_DTYPE); counts = np.zeros(n, dtype=np.int32); feat = np.zeros(n, dtype=np.int32)
     ca, cb = pa.as_c(), pb.as_c()
     _abi.check(L().xpbd_sat_manifold_batch(_abi.ptr(fa), _abi.ptr(fb), n, C.byref(ca), C.byref(cb), _abi.ptr(cons), _abi.ptr(counts), _abi.ptr(feat)))

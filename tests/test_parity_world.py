@@ -87,6 +87,16 @@ def test_c3_stack_parity(frames):
         assert c["manifolds"] > 0
 
 
+def test_c3_stack_far_from_the_origin():
+    """The same stacks 800 m away from the origin: fp32 positions carry ~6e-5 of rounding noise there, which the SAT
+    stage's witness cull has to absorb in its margin (it scales with the coordinates) — still bit-identical."""
+    init = scenes.c3_stack(48)
+    init["position"][:, :, 0] += 731.0
+    init["position"][:, :, 1] -= 415.0
+    _, c = _check(init, [CUBE], 40, 20)
+    assert c["manifolds"] > 0
+
+
 def test_c3_stack_long_run_stays_a_stack():
     """600 frames: parity on every world + physical sanity."""
     init = scenes.c3_stack(32)
