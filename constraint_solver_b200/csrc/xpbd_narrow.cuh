@@ -37,7 +37,7 @@ constexpr int kVertWords = 4;      // words per vertex in those arrays
 // edge table of the compile-time-sized instantiation (edge vectors of A, their feet, edge vectors of B)
 constexpr int kEdgeTableMax = 36;
 constexpr int kEdgeQueueWords = 4 * (64 + kEdgeTableMax);        // whole warp on one pair: 64-entry queue + table
-constexpr int kEdgeQueueWordsHalf = 4 * (32 + kEdgeTableMax);    // 16 lanes on one pair: 32-entry queue + table
+constexpr int kEdgeQueueWordsHalf = 4 * (36 + kEdgeTableMax);    // 16 lanes on one pair: 32-entry queue (culled query: 144 pair indices) + table
 
 // (value, index) arg-max across the warp: larger value wins, equal values -> lower index (the serial scan
 // keeps the FIRST strict maximum), index < 0 = "no candidate".  All lanes receive the result.
@@ -353,10 +353,14 @@ XD void edge_query_culled_t(const int2* EA, const int2* EB, int nA_rt, int nEa_r
     int bi = -1;
     const int nA = NVA ? NVA : nA_rt, nB = NVB ? NVB : nB_rt;
     const int nEb = NEB ? NEB : nEb_rt, nPairs = (NEA ? NEA : nEa_rt) * nEb;
-    int* Qi = reinterpret_cast<int*>(Q);  // survivor queue: kQueueCap entries (ia << 16 | jb) in the words ahead of the edge table
-    constexpr int kQueueCap = 4 * 2 * LG;
     constexpr bool kTable = NEA > 0 && NEB > 0 && 2 * NEA + NEB <= kEdgeTableMax;
-    float* EV = Q + 4 * 2 * LG;  // [0, NEA) edge_a | [NEA, 2 NEA) foot | [2 NEA, 2 NEA + NEB) edge_b
+    // Survivor queue (pair indices ia << 16 | jb) in the words ahead of the edge table.  When the hull sizes are known
+    // at compile time and every pair fits (cube pair: 144), the scan never has to drain it.
+    constexpr int kRegionWords = LG == 32 ? kEdgeQueueWords : kEdgeQueueWordsHalf;
+    constexpr bool kNoDrain = kTable && NEA * NEB <= kRegionWords - 4 * kEdgeTableMax;
+    constexpr int kQueueCap = kNoDrain ? kRegionWords - 4 * kEdgeTableMax : 4 * 2 * LG;
+    int* Qi = reinterpret_cast<int*>(Q);
+    float* EV = Q + kQueueCap;  // [0, NEA) edge_a | [NEA, 2 NEA) foot | [2 NEA, 2 NEA + NEB) edge_b
     if (kTable) {
         for (int t = lane; t < NEA + NEB; t += LG) {
             if (t < NEA) {
@@ -394,59 +398,63 @@ XD void edge_query_culled_t(const int2* EA, const int2* EB, int nA_rt, int nEa_r
         const float distance = fsub(sb, disp);
         if (distance > best || (distance == best && e < bi)) { best = distance; bi = e; }
     };
+    auto drain_once = [&](int& qn) {
+        __syncwarp();
+        const int take = qn < LG ? qn : LG;
+        qn -= take;
+        if (lane < take) exact_pair(Qi[qn + lane]);
+        __syncwarp();
+    };
     const float tm = fabsf(cull.T) + cull.M;
     const float K = tm * tm, Kf = cull.M * cull.M;
-    auto dcA_of = [&](V3 c) { return dot(c, CA); };
     int qn = 0;  // uniform across the lane group
 #ifdef XPBD_CULL_STATS
     int n_kept = 0;
 #endif
     const int step_a = LG / nEb, step_b = LG - step_a * nEb;  // advancing the flat pair index by LG
-    const unsigned below_me = (1u << lane) - 1u;
+    // a lane group's share of a full-warp ballot, and the lanes of the group below this one
+    const unsigned grp_mask = LG == 32 ? 0xffffffffu : (((1u << (LG & 31)) - 1u) << gshift);
+    const unsigned below_me = ((1u << lane) - 1u) << gshift;
     int ia = lane / nEb, jb = lane - ia * nEb;
-#pragma unroll 1
+#ifndef XPBD_CULL_UNROLL
+#define XPBD_CULL_UNROLL 1
+#endif
+    constexpr int kCullUnroll = XPBD_CULL_UNROLL;
+#pragma unroll kCullUnroll
     for (int e0 = 0; e0 < nPairs; e0 += LG) {
-        const int e = e0 + lane;
         bool keep = false;
-        if (e0 + LG <= nPairs || e < nPairs) {
+        if ((NEA * NEB > 0 && (NEA * NEB) % LG == 0) || e0 + LG <= nPairs || e0 + lane < nPairs) {
             V3 foot, edge_a, edge_b;
             load_pair(ia, jb, foot, edge_a, edge_b);
             const V3 c = cross(edge_a, edge_b);
             const float c2 = dot(c, c);
             const float df = dot(c, foot);
-            const float f = df - dcA_of(c);
+            const float f = df - dot(c, CA);
             const float u1 = dot(c, cull.w1) - df, u2 = dot(c, cull.w2) - df;
             const float us = f < 0.0f ? -fmaxf(u1, u2) : fminf(u1, u2);  // the smaller of the two bounds, flipped like the axis
             // (c2 > 1e-24: below that |c|^2 loses precision and the normalised axis is no longer unit length — left to stage 2)
             const bool below = us < 0.0f && fmul(us, us) > fmul(K, c2) && fmul(f, f) > fmul(Kf, c2) && c2 > 1e-24f;
             keep = !below && c2 > 0.0f;
         }
-        const unsigned m = LG == 32 ? __ballot_sync(0xffffffffu, keep) : ((__ballot_sync(0xffffffffu, keep) >> gshift) & ((1u << (LG & 31)) - 1u));
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
         if (keep) Qi[qn + __popc(m & below_me)] = (ia << 16) | jb;
         ia += step_a; jb += step_b;
         if (jb >= nEb) { jb -= nEb; ++ia; }
-        qn += __popc(m);
+        qn += __popc(m & grp_mask);
 #ifdef XPBD_CULL_STATS
-        n_kept += __popc(m);
+        n_kept += __popc(m & grp_mask);
 #endif
-        __syncwarp();
-        // Survivors are few, so they are left in the queue until the scan is over and then processed LG at a time (full
-        // lane groups; two halves in lockstep stay in step) — only a queue about to overflow is drained early.
-        const bool drain = LG == 32 ? qn > kQueueCap - LG : __any_sync(0xffffffffu, qn > kQueueCap - LG);
-        if (drain) {
-            const int take = qn < LG ? qn : LG;
-            qn -= take;
-            if (lane < take) exact_pair(Qi[qn + lane]);
-            __syncwarp();
+        if (!kNoDrain) {
+            // Survivors are few, so they stay queued until the scan is over and are then processed LG at a time (full lane
+            // groups; two halves in lockstep stay in step) — only a queue about to overflow is drained early.
+            const bool drain = LG == 32 ? qn > kQueueCap - LG : __any_sync(0xffffffffu, qn > kQueueCap - LG);
+            if (drain) drain_once(qn);
         }
     }
     for (;;) {
         const bool more = LG == 32 ? qn > 0 : __any_sync(0xffffffffu, qn > 0);
         if (!more) break;
-        const int take = qn < LG ? qn : LG;
-        qn -= take;
-        if (lane < take) exact_pair(Qi[qn + lane]);
-        __syncwarp();
+        drain_once(qn);
     }
 #ifdef XPBD_CULL_STATS
     if (lane == 0) { atomicAdd(&g_cull_stats[0], 1ull); atomicAdd(&g_cull_stats[1], (unsigned long long)n_kept); atomicAdd(&g_cull_stats[2], (unsigned long long)nPairs); }
