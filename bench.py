@@ -41,6 +41,8 @@ WORKLOADS = {
 # sweep (configs[4]: the same worlds sharded over 1/2/4/8 GPUs) are quoted on.  `--workload c2` is configs[1].
 DEFAULT_WORKLOAD = "c3"
 BYTES_PER_BODY_PER_STEP = 204  # 38 floats read + 13 written
+SAT_FLOPS_PER_PAIR_EXECUTED = 9146.0      # cube-cube candidate, culled edge query (ncu, profiles/r01j_stage_sat.txt)
+SAT_FLOPS_PER_PAIR_BRUTE_FORCE = 17480.0  # the same candidate through the reference's full edge-pair scan (profiles/r01h_stage_sat.txt)
 
 
 def measured_peaks():
@@ -359,19 +361,23 @@ def main():
                 "share_of_step": stage_ms[1] / max(sum(stage_ms), 1e-9),
                 "step": line["roofline"],
                 "note": "dominant kernel of the staged pipeline, timed ALONE (sub-batches = 1) with CUDA events on the batch stream inside the library; "
-                        "FP32-issue bound (C3: 569 FADD/FMUL/FFMA of 1 190 warp-instructions per pair, DESIGN.md section 5), so the HBM fraction is small by construction",
+                        "issue bound (C3: 372 FADD/FMUL/FFMA of 880 warp-instructions per pair, DESIGN.md section 5), so the HBM fraction is small by construction",
             }
             if "fp32" in line["roofline"]["step"]:
                 line["roofline"]["fp32"] = line["roofline"]["step"].pop("fp32")
                 if args.workload == "c3":
-                    # FP32 work of one cube-cube candidate = 17 480 thread-level flops (FADD + FMUL + 2 x FFMA, ncu SASS page
-                    # of stage_sat_cubes_kernel, profiles/r01h_stage_sat.txt / DESIGN.md section 5):
-                    # the arithmetic of the reference's brute-force face + edge queries, nothing recomputed.
+                    # FP32 work of one cube-cube candidate, thread-level flops (FADD + FMUL + 2 x FFMA) from the ncu SASS page of
+                    # stage_sat_cubes_kernel: 9 146 executed with the witness cull (profiles/r01j_stage_sat.txt), 17 480 for
+                    # the reference's brute-force face + edge queries (profiles/r01h_stage_sat.txt); DESIGN.md section 5.
                     fp = line["roofline"]["fp32"]
-                    fp["flops_per_pair"] = 17480.0
-                    fp["achieved"] = cand_pairs * 17480.0 / (stage_ms[1] * 1e-3) / 1e12
+                    fp["flops_per_pair"] = SAT_FLOPS_PER_PAIR_EXECUTED
+                    fp["achieved"] = cand_pairs * SAT_FLOPS_PER_PAIR_EXECUTED / (stage_ms[1] * 1e-3) / 1e12
                     fp["frac"] = fp["achieved"] / fp["peak"]
                     fp["kernel"] = sat_kernel
+                    fp["brute_force_flops_per_pair"] = SAT_FLOPS_PER_PAIR_BRUTE_FORCE
+                    fp["brute_force_equivalent"] = cand_pairs * SAT_FLOPS_PER_PAIR_BRUTE_FORCE / (stage_ms[1] * 1e-3) / 1e12
+                    fp["note"] = ("executed flops: the witness cull drops ~89 % of the edge pairs before the reference arithmetic; "
+                                  "brute_force_equivalent = the rate at which the reference's full scan would have to run to finish in the same time")
         # roofline.traffic: DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/)
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:

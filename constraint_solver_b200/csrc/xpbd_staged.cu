@@ -821,11 +821,11 @@ static int ensure_staged(xpbd_batch* b, StagedState*& out) {
 }
 
 // Number of world ranges a step call runs concurrently: the caller's choice (xpbd_batch_set_sub_batches), else
-// XPBD_SUB_BATCHES, else one range per 2^18 bodies up to 4 (C3 and C4: 4).
+// XPBD_SUB_BATCHES, else one range per 2^18 bodies (rounded) up to 4 (C3 and C4: 4).
 static int pick_sub_batches(const xpbd_batch* b) {
     int k = b->sub_batches;
     if (k <= 0) { if (const char* e = std::getenv("XPBD_SUB_BATCHES")) k = std::atoi(e); }
-    if (k <= 0) k = (int)std::min<int64_t>(4, b->n_bodies >> 18);
+    if (k <= 0) k = (int)std::min<int64_t>(4, (b->n_bodies + (1 << 17)) >> 18);  // rounded: C3's 10^6 bodies -> 4
     k = std::max(1, std::min(k, kMaxSubBatches));
     return (int)std::min<int64_t>(k, std::max<int64_t>(1, b->desc.n_worlds));
 }
