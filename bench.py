@@ -279,16 +279,14 @@ def main():
     pin_out = torch.empty((n_bodies, 13), dtype=torch.float32, pin_memory=True)
     w.download_dynamic_ptr(pin_in.data_ptr(), 0, n_worlds)
     for _ in range(2):
-        w.upload_dynamic_ptr(pin_in.data_ptr(), 0, n_worlds)
-        w.integrate(dt, S, 1, sync=False)
-        w.download_dynamic_ptr(pin_out.data_ptr(), 0, n_worlds)
+        w.integrate_host_ptr(dt, S, 1, pin_in.data_ptr(), pin_out.data_ptr(), sync=True)
         pin_in, pin_out = pin_out, pin_in
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        w.upload_dynamic_ptr(pin_in.data_ptr(), 0, n_worlds)
-        w.integrate(dt, S, 1, sync=False)
-        w.download_dynamic_ptr(pin_out.data_ptr(), 0, n_worlds)  # synchronises: the caller owns the result
+        # xpbd_batch_step_host_f32: H2D of the state, one frame, D2H of the result (per world range, so the copies of one
+        # range run under the kernels of the others), then xpbd_batch_sync: the caller owns the result before the next step
+        w.integrate_host_ptr(dt, S, 1, pin_in.data_ptr(), pin_out.data_ptr(), sync=True)
         pin_in, pin_out = pin_out, pin_in
     barrier()
     e2e_s = time.perf_counter() - t0
@@ -321,7 +319,7 @@ def main():
                        "fma": "off (bit parity with the fp32 oracle)",
                        "sub_batches": f"{sub_batches} contiguous world ranges per GPU stepped concurrently on {sub_batches} streams (xpbd_batch_set_sub_batches, automatic)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": io_bytes, "d2h_bytes_per_step": io_bytes,
-                    "what": "xpbd_batch_upload_dynamic_f32 (pinned host) + xpbd_batch_step + xpbd_batch_download_dynamic_f32, wall clock"},
+                    "what": "xpbd_batch_step_host_f32 (pinned host buffers: H2D of every body's dynamic state, one frame, D2H of the result) + xpbd_batch_sync per step, wall clock"},
             "gpu_launches": args.steps * stats["kernel_launches"],
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",

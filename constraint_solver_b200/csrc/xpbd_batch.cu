@@ -43,12 +43,15 @@ int ensure_stage(xpbd_batch* b) {
 namespace xpbd {
 // Multi-body path selection.  XPBD_WORLD_PATH=fused|staged overrides; default: the staged pipeline for batches
 // large enough to fill the GPU per stage, the fused single-launch kernel for small ones (latency-bound).
-int step_world(xpbd_batch* b, float frame_dt, int substeps, int n_frames) {
+bool world_path_is_staged(const xpbd_batch* b) {
     const char* v = getenv("XPBD_WORLD_PATH");
     bool staged = b->desc.n_worlds >= 4096;
     if (v && !strcmp(v, "fused")) staged = false;
     if (v && !strcmp(v, "staged")) staged = true;
-    return staged ? step_world_staged(b, frame_dt, substeps, n_frames) : step_world_fused(b, frame_dt, substeps, n_frames);
+    return staged;
+}
+int step_world(xpbd_batch* b, float frame_dt, int substeps, int n_frames) {
+    return world_path_is_staged(b) ? step_world_staged(b, frame_dt, substeps, n_frames) : step_world_fused(b, frame_dt, substeps, n_frames);
 }
 }  // namespace xpbd
 
@@ -324,20 +327,46 @@ int xpbd_batch_upload_dynamic_f32(xpbd_batch* b, int64_t first_world, int64_t n_
     return XPBD_OK;  // ordered before any later launch on the batch stream
 }
 
+static int step_common(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_frames, const float* in, float* out);
+
 int xpbd_batch_step(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_frames) {
+    return step_common(b, dt, substep_count, n_frames, nullptr, nullptr);
+}
+
+int xpbd_batch_step_host_f32(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_frames, const float* in, float* out) {
+    return step_common(b, dt, substep_count, n_frames, in, out);
+}
+
+static int step_common(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_frames, const float* in, float* out) {
     if (int rc = check_batch(b)) return rc;
     if (substep_count <= 0 || n_frames <= 0) return fail(XPBD_ERR_INVALID, "substep_count and n_frames must be positive");
     if (!(dt > 0.0) || !std::isfinite(dt)) return fail(XPBD_ERR_INVALID, "dt must be positive and finite");
     if (int rc = bind_device(b)) return rc;
     if (int rc = finalize_hulls(b)) return rc;
+    if (in || out) { if (int rc = ensure_dyn_stage(b)) return rc; }
     XPBD_CUDA_TRY(cudaEventRecord(b->ev_start, b->stream));
     XPBD_CUDA_TRY(cudaMemsetAsync(b->d_counters, 0, 4 * sizeof(unsigned long long), b->stream));
     b->stage_timed = false;
     b->last.sub_batches = 1;
     const bool world_path = b->desc.body_body_contacts != 0 || b->desc.joints_per_world > 0;
+    // Host buffers: the staged pipeline consumes them per world range (copies on the range's stream) and clears the
+    // pointers; every other path copies the whole batch on the batch stream around its kernels.
+    b->io_in = in;
+    b->io_out = out;
+    if (b->io_in && !(world_path && staged_takes_host_buffers(b))) {
+        XPBD_CUDA_TRY(cudaMemcpyAsync(b->d_dyn_stage, b->io_in, (size_t)b->n_bodies * 13 * sizeof(float), cudaMemcpyHostToDevice, b->stream));
+        launch_dyn_unpack(b->d_dyn_stage, b->arrays, 0, b->n_bodies, b->stream);
+        b->io_in = nullptr;
+    }
     int rc = world_path ? step_world(b, (float)dt, substep_count, n_frames)
                         : step_single(b, (float)dt, substep_count, n_frames);
-    if (rc != XPBD_OK) return rc;
+    if (rc != XPBD_OK) { b->io_in = nullptr; b->io_out = nullptr; return rc; }
+    if (b->io_out) {  // not consumed per range
+        launch_dyn_pack(b->arrays, b->d_dyn_stage, 0, b->n_bodies, b->stream);
+        XPBD_CUDA_TRY(cudaMemcpyAsync(b->io_out, b->d_dyn_stage, (size_t)b->n_bodies * 13 * sizeof(float), cudaMemcpyDeviceToHost, b->stream));
+    }
+    b->io_in = nullptr;
+    b->io_out = nullptr;
     if (b->last.sub_batches <= 1) b->fork_needed = true;  // this step's kernels ran on the batch stream itself
     XPBD_CUDA_TRY(cudaMemcpyAsync(b->h_counters, b->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost,
                                   b->stream));

@@ -113,6 +113,9 @@ struct xpbd_batch {
     // range just continues behind its own previous frame, so the ranges drift out of phase and kernels of different
     // stages overlap (a barrier per frame would re-align them).
     bool fork_needed = true;
+    // xpbd_batch_step_host_f32: host buffers of the step call in flight (packed dynamic state, 13 floats per body)
+    const float* io_in = nullptr;
+    float* io_out = nullptr;
 };
 
 namespace xpbd {
@@ -122,6 +125,10 @@ int step_world_fused(xpbd_batch* b, float frame_dt, int substeps, int n_frames);
 int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames);  // xpbd_staged.cu
 int step_world(xpbd_batch* b, float frame_dt, int substeps, int n_frames);         // picks one of the two
 void release_world_scratch(xpbd_batch* b);
+// true when the next multi-body step call will run the staged pipeline on several world ranges (which then move
+// b->io_in / b->io_out per range, on the range streams)
+bool staged_takes_host_buffers(const xpbd_batch* b);
+bool world_path_is_staged(const xpbd_batch* b);  // XPBD_WORLD_PATH / batch size
 // adds the per-range counters of the last staged step call (valid once ev_stop has completed) to acc[0..3]
 void staged_add_range_counters(const xpbd_batch* b, unsigned long long* acc);
 }  // namespace xpbd

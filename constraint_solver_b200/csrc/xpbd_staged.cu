@@ -830,6 +830,8 @@ static int pick_sub_batches(const xpbd_batch* b) {
     return (int)std::min<int64_t>(k, std::max<int64_t>(1, b->desc.n_worlds));
 }
 
+bool staged_takes_host_buffers(const xpbd_batch* b) { return world_path_is_staged(b) && pick_sub_batches(b) > 1; }
+
 static int ensure_sub_streams(xpbd_batch* b, StagedState* st, int n_sub) {
     if (st->n_sub == n_sub && (int)st->sub_streams.size() == (n_sub > 1 ? n_sub : 0)) return XPBD_OK;
     st->release_streams();  // (destroying a stream with pending work is deferred by the runtime until it has drained)
@@ -935,6 +937,10 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
             Q.counters = st->d_range_counters + 4 * k;
             if (fork) XPBD_CUDA_TRY(cudaStreamWaitEvent(stream, st->ev_fork, 0));
             XPBD_CUDA_TRY(cudaMemsetAsync(Q.counters, 0, 4 * sizeof(unsigned long long), stream));
+            if (b->io_in) {  // xpbd_batch_step_host_f32: this range's state from the host, under the other ranges' kernels
+                XPBD_CUDA_TRY(cudaMemcpyAsync(b->d_dyn_stage + 13 * g0, b->io_in + 13 * g0, (size_t)(nw * B) * 13 * sizeof(float), cudaMemcpyHostToDevice, stream));
+                launch_dyn_unpack(b->d_dyn_stage + 13 * g0, b->arrays, g0, nw * B, stream);
+            }
         }
         XPBD_CUDA_TRY(cudaMemsetAsync(S.overflow, 0, (size_t)nw * sizeof(int), stream));
         const int grid_prepare = (int)std::min<int64_t>((nw + worlds_per_block - 1) / worlds_per_block, (int64_t)st->n_sm * st->occ_prepare);
@@ -956,6 +962,10 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
             stage_solve_kernel<<<grid_solve, 128, 0, stream>>>(Q);
             if (timed) cudaEventRecord(b->ev_stage[4], stream);
         }
+        if (n_sub > 1 && b->io_out) {  // ... and its result back to the host
+            launch_dyn_pack(b->arrays, b->d_dyn_stage + 13 * g0, g0, nw * B, stream);
+            XPBD_CUDA_TRY(cudaMemcpyAsync(b->io_out + 13 * g0, b->d_dyn_stage + 13 * g0, (size_t)(nw * B) * 13 * sizeof(float), cudaMemcpyDeviceToHost, stream));
+        }
         if (n_sub > 1) {
             XPBD_CUDA_TRY(cudaMemcpyAsync(st->h_range_counters + 4 * k, Q.counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
             XPBD_CUDA_TRY(cudaEventRecord(st->sub_done[k], stream));
@@ -963,6 +973,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
         }
     }
     b->fork_needed = false;
+    if (n_sub > 1) { b->io_in = nullptr; b->io_out = nullptr; }  // consumed per range
     b->last.sub_batches = n_sub;
     b->stage_timed = true;
     XPBD_CUDA_TRY(cudaGetLastError());

@@ -165,6 +165,23 @@ class Worlds:
         if sync:
             self.sync()
 
+    def integrate_host_ptr(self, dt: float, substep_count: int, n_frames: int, in_ptr: int, out_ptr: int, sync: bool = True) -> None:
+        """World::integrate for callers whose state lives in host memory: packed dynamic state in (13 floats per body,
+        0 = keep the device state), the same out (0 = none); one call, copies pipelined under the kernels per world range."""
+        _abi.check(self._lib.xpbd_batch_step_host_f32(self._h, float(dt), int(substep_count), int(n_frames),
+                                                      C.c_void_p(in_ptr or None), C.c_void_p(out_ptr or None)))
+        if sync:
+            self.sync()
+
+    def integrate_host(self, dyn_in: np.ndarray | None, dt: float, substep_count: int = SUBSTEPS, n_frames: int = 1) -> np.ndarray:
+        """Numpy form of integrate_host_ptr: returns the new packed dynamic state (n_worlds x bodies_per_world x 13 float32)."""
+        out = np.empty((self.n_worlds, self.bodies_per_world, 13), dtype=np.float32)  # download_dynamic's shape
+        if dyn_in is not None:
+            dyn_in = np.ascontiguousarray(dyn_in, dtype=np.float32)
+            assert dyn_in.size == self.n_bodies * 13
+        self.integrate_host_ptr(dt, substep_count, n_frames, 0 if dyn_in is None else dyn_in.ctypes.data, out.ctypes.data)
+        return out
+
     def sync(self) -> None:
         _abi.check(self._lib.xpbd_batch_sync(self._h))
 

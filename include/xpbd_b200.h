@@ -181,6 +181,14 @@ int xpbd_batch_upload_dynamic_f32(xpbd_batch* batch, int64_t first_world, int64_
  * (World::integrate, src/world.rs:34-43, is one frame with substep_count 25).
  * Asynchronous on the batch stream; all substeps of all frames run fused in one launch. */
 int xpbd_batch_step(xpbd_batch* batch, double dt, int32_t substep_count, int32_t n_frames);
+/* The same for callers whose state lives in HOST memory (the reference's `World` values, src/app.rs:204-215): uploads
+ * the packed dynamic state `in` (13 floats per body, the layout of xpbd_batch_upload_dynamic_f32; NULL = keep the device
+ * state), steps, and downloads the result into `out` (NULL = none).  Asynchronous: `out` is valid after xpbd_batch_sync.
+ * When the staged pipeline runs several world ranges, each range's copies sit on that range's stream, so the host
+ * copies of one range run under the kernels of the others.  `in` / `out` should be page-locked; pageable memory works but
+ * serialises the copies. */
+int xpbd_batch_step_host_f32(xpbd_batch* batch, double dt, int32_t substep_count, int32_t n_frames, const float* in,
+                             float* out);
 int xpbd_batch_sync(xpbd_batch* batch);
 /* Valid after xpbd_batch_sync. */
 int xpbd_batch_last_stats(xpbd_batch* batch, xpbd_step_stats* out);

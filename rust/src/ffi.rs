@@ -113,6 +113,7 @@ extern "C" {
     pub fn xpbd_batch_set_joints(batch: *mut xpbd_batch, first: i64, n: i64, joints: *const xpbd_joint) -> c_int;
     pub fn xpbd_batch_set_stream(batch: *mut xpbd_batch, cuda_stream: *mut c_void) -> c_int;
     pub fn xpbd_batch_set_sub_batches(batch: *mut xpbd_batch, count: i32) -> c_int;
+    pub fn xpbd_batch_step_host_f32(batch: *mut xpbd_batch, dt: f64, substep_count: i32, n_frames: i32, input: *const f32, output: *mut f32) -> c_int;
     pub fn xpbd_batch_upload(batch: *mut xpbd_batch, first: i64, n: i64, rigids: *const xpbd_rigid) -> c_int;
     pub fn xpbd_batch_download(batch: *mut xpbd_batch, first: i64, n: i64, rigids: *mut xpbd_rigid) -> c_int;
     pub fn xpbd_batch_upload_broadcast(batch: *mut xpbd_batch, world_bodies: *const xpbd_rigid) -> c_int;

@@ -232,6 +232,32 @@ def test_sub_batches_back_to_back_step_calls(world_path):
     assert np.array_equal(xo.rigid38(got), cpu.astype(np.float64))
 
 
+@pytest.mark.parametrize("k", [1, 4])
+def test_step_host_equals_upload_step_download(world_path, k):
+    """xpbd_batch_step_host_f32 (state in host memory: upload + step + download in one call, the copies pipelined per
+    world range) gives the same bits as the three separate calls, frame after frame."""
+    n = 131
+    init = scenes.c3_stack(n)
+    with cs.Worlds(n, 10, body_body_contacts=True) as a, cs.Worlds(n, 10, body_body_contacts=True) as b:
+        for w in (a, b):
+            w.add_hull(CUBE)
+            w.set_sub_batches(k)
+            w.upload(init)
+        dyn = a.download_dynamic()
+        ref = dyn.copy()
+        for _ in range(8):
+            b.upload_dynamic(ref)
+            b.integrate(DT, 20, 1)
+            ref = b.download_dynamic()
+            dyn = a.integrate_host(dyn, DT, 20, 1)
+            assert np.array_equal(dyn, ref)
+        # NULL input keeps the device state; NULL output only steps
+        a.integrate_host_ptr(DT, 20, 1, 0, 0)
+        b.integrate(DT, 20, 1)
+        assert np.array_equal(a.download_dynamic(), b.download_dynamic())
+    assert np.abs(ref).max() > 0
+
+
 def test_sub_batches_stats_sum_over_ranges(world_path):
     """constraints / candidate_pairs of xpbd_step_stats are totals over all world ranges."""
     if world_path == "fused":
