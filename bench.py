@@ -256,7 +256,7 @@ def main():
     # the last substep of a step call; xpbd_step_stats.stage_ms), averaged over a few extra untimed step calls
     stage_ms, cand_pairs = None, 0
     sub_batches = int(stats.get("sub_batches", 1))
-    if stats["kernel_launches"] > 1:
+    if body_body or joints is not None:  # the staged multi-body pipeline
         acc = np.zeros(4)
         w.set_sub_batches(1)  # each stage kernel timed ALONE: one chain of launches on the batch stream (the timed region above
         #                       runs `sub_batches` world ranges concurrently, so there a kernel's wall time includes its neighbours)

@@ -134,6 +134,10 @@ int xpbd_batch_destroy(xpbd_batch* b) {
         if (b->stage_free[s]) cudaEventDestroy(b->stage_free[s]);
     }
     if (b->d_dyn_stage) cudaFree(b->d_dyn_stage);
+    for (int s = 0; s < 2; ++s)
+        if (b->d_order[s]) cudaFree(b->d_order[s]);
+    if (b->d_contact_count) cudaFree(b->d_contact_count);
+    if (b->d_order_bins) cudaFree(b->d_order_bins);
     if (b->d_counters) cudaFree(b->d_counters);
     if (b->h_counters) cudaFreeHost(b->h_counters);
     if (b->ev_start) cudaEventDestroy(b->ev_start);

@@ -106,6 +106,12 @@ struct xpbd_batch {
     xpbd_step_stats last{};
     bool stepped = false;
     void* world_scratch = nullptr;  // owned by the multi-body path
+    // single-body path: thread -> body permutation that groups bodies by their ground-contact count (xpbd_single.cu)
+    int32_t* d_order[2] = {nullptr, nullptr};  // [cur] read by the step kernel, [cur ^ 1] written by the regrouping pass
+    int order_cur = 0;
+    bool order_valid = false;
+    uint8_t* d_contact_count = nullptr;  // per body: ground contacts in the last substep of the last step call
+    int32_t* d_order_bins = nullptr;     // 32 ints: histogram, then cursors
     int sub_batches = 0;            // xpbd_batch_set_sub_batches: 0 = automatic
     // Set by every call that enqueues work on `stream` touching the batch's device memory (uploads, downloads, hull /
     // joint tables, a new stream); cleared by a step call.  When the staged pipeline runs several world ranges on its

@@ -86,6 +86,30 @@ def test_c2_perturbed_sample(frames):
         assert w.stats()["constraints"] == ncons
 
 
+@pytest.mark.parametrize("n", [4097, 70_000])
+def test_c2_regrouped_bodies_frame_by_frame(n, monkeypatch):
+    """Regrouping (xpbd_single.cu): after every step call the thread -> body permutation is rebuilt from the contact
+    counts, so from the second call on every body is stepped by a different thread.  Per-frame calls over a settling
+    scene (airborne, tumbling and resting bodies mixed), ragged body count; bit-identical to the oracle, and the
+    constraint count of every call matches.  n = 70 000 takes the automatic choice (>= 2^16 bodies), 4 097 forces it."""
+    if n < (1 << 16):
+        monkeypatch.setenv("XPBD_SINGLE_REGROUP", "1")
+    frames = 40
+    init = scenes.c2_perturbed(n)
+    cpu, ncons = _oracle(init, frames)
+    total = 0
+    with cs.Worlds(n) as w:
+        w.add_hull(CUBE); w.upload(init)
+        for _ in range(frames):
+            w.integrate(DT, 25, 1)
+            st = w.stats()
+            total += st["constraints"]
+            assert st["kernel_launches"] == 4  # step kernel + histogram, scan, scatter
+        pos, rot, exact = parity.compare(w.download(), cpu)
+    assert exact, (pos, rot)
+    assert total == ncons
+
+
 def test_c2_full_size_properties_and_sampled_parity():
     """C2 at BASELINE size (2^20 worlds): sampled worlds vs the oracle + size-independent properties
     (identical inputs -> identical outputs; unit quaternions; no NaN; nothing below the ground by more than slop)."""
