@@ -283,7 +283,7 @@ XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int 
 // Two witnesses are used (witness_vertices: B's deepest vertex below A's best face and a second deep vertex far from it);
 // any vertices would be valid, these sit in the contact region, where they cull most.
 #ifdef XPBD_CULL_STATS
-__device__ unsigned long long g_cull_stats[3];  // edge queries, pairs kept by stage 1, pairs seen (debug builds: scripts/cull_stats.sh)
+__device__ unsigned long long g_cull_stats[3 + 40];  // + histogram of pairs kept per query (capped at 39)  // edge queries, pairs kept by stage 1, pairs seen (debug builds: scripts/cull_stats.sh)
 #endif
 struct EdgeCull {
     float T;    // min(0, kRelEdge * face_max + kAbsTol)
@@ -457,7 +457,7 @@ XD void edge_query_culled_t(const int2* EA, const int2* EB, int nA_rt, int nEa_r
         drain_once(qn);
     }
 #ifdef XPBD_CULL_STATS
-    if (lane == 0) { atomicAdd(&g_cull_stats[0], 1ull); atomicAdd(&g_cull_stats[1], (unsigned long long)n_kept); atomicAdd(&g_cull_stats[2], (unsigned long long)nPairs); }
+    if (lane == 0) { atomicAdd(&g_cull_stats[0], 1ull); atomicAdd(&g_cull_stats[1], (unsigned long long)n_kept); atomicAdd(&g_cull_stats[2], (unsigned long long)nPairs); atomicAdd(&g_cull_stats[3 + (n_kept < 39 ? n_kept : 39)], 1ull); }
 #endif
     if (LG == 32) warp_argmax_first(best, bi); else warp_argmax_first_halves(best, bi, gshift);
     out_d = best;

@@ -854,9 +854,9 @@ static int ensure_sub_streams(xpbd_batch* b, StagedState* st, int n_sub) {
 }
 
 #ifdef XPBD_CULL_STATS
-extern "C" void xpbd_debug_cull_stats(unsigned long long out[3]) {  // debug builds only
+extern "C" void xpbd_debug_cull_stats(unsigned long long out[43]) {  // debug builds only
     cudaDeviceSynchronize();
-    cudaMemcpyFromSymbol(out, g_cull_stats, 3 * sizeof(unsigned long long));
+    cudaMemcpyFromSymbol(out, g_cull_stats, 43 * sizeof(unsigned long long));
 }
 #endif
 

@@ -13,7 +13,7 @@ import bench
 
 lib = _abi.load()
 def stats():
-    out = (C.c_ulonglong * 3)()
+    out = (C.c_ulonglong * 43)()
     lib.xpbd_debug_cull_stats(out)
     return list(out)
 
@@ -32,5 +32,7 @@ for wl, n in (("c3", 4096), ("c4", 512)):
     w.integrate(1 / 60, cfg["substeps"], 5)
     b = stats()
     q, kept, seen = (b[i] - a[i] for i in range(3))
+    hist = [b[3 + i] - a[3 + i] for i in range(40)]
+    print("   kept-per-query histogram (%):", {i: round(100.0 * h / max(q, 1), 1) for i, h in enumerate(hist) if h})
     print(f"{wl}: {q} edge queries, {seen / max(q,1):.1f} edge pairs each, {kept / max(q,1):.2f} kept by stage 1 ({100.0 * kept / max(seen,1):.1f} %)")
     w.close()
