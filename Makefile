@@ -12,8 +12,12 @@ lib: $(LIB)
 $(LIB): $(SRCS) $(HDRS)
 	mkdir -p $(dir $(LIB))
 	$(NVCC) $(NVCCFLAGS) $(EXTRA) -o $@ $(SRCS)
+# debug build that counts how many edge pairs survive the SAT stage's witness cull (scripts/cull_stats.py)
+stats:
+	mkdir -p constraint_solver_b200/lib/debug
+	$(NVCC) $(NVCCFLAGS) -DXPBD_CULL_STATS -o constraint_solver_b200/lib/debug/libxpbd_b200_stats.so $(SRCS)
 oracle:
 	$(MAKE) -C oracle
 clean:
 	rm -rf constraint_solver_b200/lib oracle/_build
-.PHONY: all lib oracle clean
+.PHONY: all lib oracle clean stats
