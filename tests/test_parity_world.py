@@ -258,6 +258,14 @@ def test_step_host_equals_upload_step_download(world_path, k):
     assert np.abs(ref).max() > 0
 
 
+def test_sub_batches_argument_is_validated():
+    with cs.Worlds(8, 2, body_body_contacts=True) as w:
+        for bad in (-1, 9):
+            with pytest.raises(_abi.XpbdError):
+                w.set_sub_batches(bad)
+        w.set_sub_batches(0)
+
+
 def test_sub_batches_stats_sum_over_ranges(world_path):
     """constraints / candidate_pairs of xpbd_step_stats are totals over all world ranges."""
     if world_path == "fused":
