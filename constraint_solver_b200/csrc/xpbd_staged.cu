@@ -388,8 +388,18 @@ __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_kernel(Sta
     float* W = reinterpret_cast<float*>(smem) + P.hull_blob_bytes / 4 + (size_t)warp * sat_words_per_warp(maxV);
     float* Qregion = W + 6 * kVertWords * maxV;
     const unsigned count = *P.S.work_count;
-    for (unsigned it = blockIdx.x * nwarps + warp; it < count; it += gridDim.x * nwarps)
+    // Mixed hulls: a candidate costs anything between ~300 instructions (separated by the first face query) and tens of
+    // thousands (two 32-vertex hulls in contact), and there are only a few per warp — candidates are handed out one at a
+    // time through a cursor (work_count[2], reset with the counter) instead of a fixed stride, so that no warp is left
+    // with several heavy ones.  The order in which candidates are taken cannot influence results (own slot each).
+    (void)nwarps;
+    for (;;) {
+        unsigned it = 0;
+        if (lane == 0) it = atomicAdd(P.S.work_count + 2, 1u);
+        it = __shfl_sync(0xffffffffu, it, 0);
+        if (it >= count) break;
         sat_single<kCull>(P, T, P.S.worklist[it], W, W + kVertWords * maxV, W + 2 * kVertWords * maxV, Qregion, lane);
+    }
 }
 
 // Batches in which every registered hull is cube-shaped (8 vertices, 12 edges, 6 quads): two candidates per warp.
@@ -589,6 +599,7 @@ __global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel
     if (blockIdx.x == 0 && threadIdx.x == 0) {  // consumed by sat + manifold; the next substep appends again
         if (P.cand_stat) atomicAdd(P.cand_stat, (unsigned long long)*P.S.work_count);  // statistics (summed over sub-batches)
         *P.S.work_count = 0;
+        P.S.work_count[2] = 0;  // stage_sat_kernel's cursor
     }
     const StepConsts sc = P.sc;
     // grid-stride over worlds: the host may launch fewer blocks than worlds / 64 so that the worlds in flight
