@@ -68,13 +68,14 @@ struct StagedParams {
     float friction;
     int body_body;
     int pair_table_len;  // B(B-1)/2 when stage_prepare keeps the pair table in shared memory, else 0
+    int compact_verts;   // hulls with different vertex counts: stage_prepare enumerates (body, vertex) through a prefix sum
     unsigned long long* counters;  // [0] constraints, [1] overflow worlds, [2] tma fallbacks
     unsigned long long* cand_stat;  // non-null on the last substep of a step call: += candidates of this launch (statistics)
 };
 
 // ---- stage 1: prepare (warp per world) -----------------------------------------------------------------
-// per-warp shared scratch, words per body: fpos 3, pfpos 3, finvp 3, cen 3, rot 4, prot 4, hull 1
-constexpr int kPrepWordsPerBody = 21;
+// per-warp shared scratch, words per body: fpos 3, pfpos 3, finvp 3, cen 3, rot 4, prot 4, hull 1, vertex offset 1
+constexpr int kPrepWordsPerBody = 22;
 
 #ifndef XPBD_PREP_MIN_BLOCKS
 #define XPBD_PREP_MIN_BLOCKS 4
@@ -102,6 +103,7 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
     float* s_fpos = W; float* s_pfpos = W + 3 * B; float* s_finvp = W + 6 * B; float* s_cen = W + 9 * B;
     float* s_rot = W + 12 * B; float* s_prot = W + 16 * B;
     int* s_hull = reinterpret_cast<int*>(W + 20 * B);
+    int* s_voff = s_hull + B;  // compact vertex enumeration: vertices of the bodies before b (mixed-hull batches)
     uint32_t* pair_table = smem + P.hull_blob_bytes / 4 + (size_t)nwarps * NG * kPrepWordsPerBody * B;
     const int n_table = P.pair_table_len;
     if (n_table > 0) {
@@ -145,20 +147,50 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
         int n_ground = 0;
         {
             float* gc = P.S.gcons + (size_t)world * P.S.capG * kGroundWords;
-            int b = 0, v = gl;
-            for (int t0 = 0; t0 < B * maxV; t0 += G) {
-                while (v >= maxV) { v -= maxV; ++b; }
+            // Lanes over (body, vertex) in body-major / vertex order.  Batches whose hulls all have maxV vertices walk the
+            // B x maxV grid directly; mixed batches (C4: 4 ... 32 vertices per hull) walk a compact enumeration built from a
+            // prefix sum of the vertex counts, so that no lane is spent on the padding (C4: 64 -> ~28 rounds per world).
+            int b = 0, v = gl, total = B * maxV;
+            if (P.compact_verts) {
+                int run = 0;
+                for (int b0 = 0; b0 < B; b0 += G) {
+                    const int bb = b0 + gl;
+                    const int nv = (valid && bb < B) ? T.desc(s_hull[bb]).n_verts : 0;
+                    int incl = nv;
+#pragma unroll
+                    for (int o = 1; o < G; o <<= 1) { const int up = __shfl_up_sync(kFull, incl, o, G); if (gl >= o) incl += up; }
+                    if (valid && bb < B) s_voff[bb] = run + incl - nv;
+                    run += __shfl_sync(kFull, incl, G - 1, G);
+                }
+                total = (int)__reduce_max_sync(kFull, (unsigned)run);  // a warp-uniform trip count (two worlds per warp when G = 16)
+                __syncwarp();
+                if (!valid || gl >= run) { b = B; }  // nothing (more) for this lane
+                else { b = 0; }
+                v = gl;  // here: the lane's flat vertex index
+            }
+            for (int t0 = 0; t0 < total; t0 += G) {
+                bool has = false;
+                int vv = 0;
+                if (P.compact_verts) {
+                    if (valid && b < B) {
+                        while (b + 1 < B && v >= s_voff[b + 1]) ++b;
+                        vv = v - s_voff[b];
+                        has = vv < T.desc(s_hull[b]).n_verts;  // false once the flat index has run past the last body
+                    }
+                } else {
+                    while (v >= maxV) { v -= maxV; ++b; }
+                    vv = v;
+                    has = valid && b < B && v < T.desc(s_hull[b < B ? b : 0]).n_verts;
+                }
                 bool below = false;
                 V3 p = v3(0.f, 0.f, 0.f);
                 Fr frame;
-                if (valid && b < B) {
+                if (has) {
                     const HullDesc& hd = T.desc(s_hull[b]);
-                    if (v < hd.n_verts) {
-                        frame.p = sld3(s_fpos, B, b); frame.q = sldq(s_rot, B, b);
-                        p = frame * T.vertex(hd, v);
-                        P.S.verts[(g0 + b) * maxV + v] = make_float4(p.x, p.y, p.z, 0.f);
-                        below = !(p.z >= 0.0f);
-                    }
+                    frame.p = sld3(s_fpos, B, b); frame.q = sldq(s_rot, B, b);
+                    p = frame * T.vertex(hd, vv);
+                    P.S.verts[(g0 + b) * maxV + vv] = make_float4(p.x, p.y, p.z, 0.f);
+                    below = !(p.z >= 0.0f);
                 }
                 const unsigned m = (__ballot_sync(kFull, below) & gmask) >> gshift;
                 if (below) {
@@ -907,6 +939,8 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
     P.friction = (float)b->desc.friction;
     P.body_body = b->desc.body_body_contacts;
     P.pair_table_len = st->pair_table_len;
+    P.compact_verts = 0;
+    for (const HostHull& h : b->hulls) if ((int)(h.vertices.size() / 3) != H.max_verts) P.compact_verts = 1;
     P.counters = b->d_counters;
     P.cand_stat = nullptr;
     const int n_sub = pick_sub_batches(b);
