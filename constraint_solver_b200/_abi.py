@@ -88,7 +88,7 @@ class StepStatsC(C.Structure):
         ("stage_ms", C.c_float * 4),
         ("candidate_pairs", C.c_uint64),
         ("sub_batches", C.c_int32),
-        ("reserved", C.c_int32),
+        ("nan_worlds", C.c_int32),
     ]
 
 
@@ -135,6 +135,7 @@ _PROTOTYPES = {
     "xpbd_face_axes_separation_batch": (C.c_int, [_VP, _VP, C.c_int64, C.POINTER(PolytopeC), C.POINTER(PolytopeC), _VP, _VP]),
     "xpbd_edge_axes_separation_batch": (C.c_int, [_VP, _VP, C.c_int64, C.POINTER(PolytopeC), C.POINTER(PolytopeC), _VP, _VP]),
     "xpbd_sat_manifold_batch": (C.c_int, [_VP, _VP, C.c_int64, C.POINTER(PolytopeC), C.POINTER(PolytopeC), _VP, _VP, _VP]),
+    "xpbd_sat_feature_batch": (C.c_int, [_VP, _VP, C.c_int64, C.POINTER(PolytopeC), C.POINTER(PolytopeC), C.c_int32, C.c_int32, _VP, _VP]),
     "xpbd_fp32_peak_microbench": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(C.c_double)]),
 }
 EXPORTED_SYMBOLS = tuple(_PROTOTYPES)

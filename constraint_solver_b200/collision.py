@@ -61,3 +61,20 @@ def sat(frames, polytopes) -> tuple[bool, list[Constraint]]:
     _abi.check(_abi.load().xpbd_sat_manifold_batch(_abi.ptr(fa), _abi.ptr(fb), 1, C.byref(ca), C.byref(cb),
                                                    _abi.ptr(out), _abi.ptr(count), _abi.ptr(feature)))
     return int(feature[0]) == 0, [Constraint.from_record(out[i]) for i in range(int(count[0]))]
+
+
+SAT_SCHEDULES = {"warp": 0, "dual": 1, "thread": 2}
+
+
+def sat_feature_batch(frames_a: np.ndarray, frames_b: np.ndarray, hull_a: Polytope, hull_b: Polytope, schedule: str = "warp",
+                      cull: bool = True) -> tuple[np.ndarray, np.ndarray]:
+    """The step's SAT stage (face query A, face query B, edge query, feature choice) on n synthetic candidate pairs,
+    through the step's own kernels (xpbd_sat_feature_batch).  frames_*: FRAME_DTYPE arrays.  Returns (feature, index)."""
+    fa = np.ascontiguousarray(frames_a, dtype=_abi.FRAME_DTYPE)
+    fb = np.ascontiguousarray(frames_b, dtype=_abi.FRAME_DTYPE)
+    assert fa.shape == fb.shape and fa.ndim == 1
+    feature = np.zeros(len(fa), dtype=np.int32); index = np.zeros(len(fa), dtype=np.int32)
+    ca, cb = hull_a.as_c(), hull_b.as_c()
+    _abi.check(_abi.load().xpbd_sat_feature_batch(_abi.ptr(fa), _abi.ptr(fb), len(fa), C.byref(ca), C.byref(cb),
+                                                  SAT_SCHEDULES[schedule], 1 if cull else 0, _abi.ptr(feature), _abi.ptr(index)))
+    return feature, index

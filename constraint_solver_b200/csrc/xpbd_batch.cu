@@ -41,17 +41,30 @@ int ensure_stage(xpbd_batch* b) {
 }  // namespace
 
 namespace xpbd {
-// Multi-body path selection.  XPBD_WORLD_PATH=fused|staged overrides; default: the staged pipeline for batches
-// large enough to fill the GPU per stage, the fused single-launch kernel for small ones (latency-bound).
-bool world_path_is_staged(const xpbd_batch* b) {
+// Multi-body path selection.  XPBD_WORLD_PATH=fused|staged forces one; default: the staged pipeline for batches
+// large enough to fill the GPU per stage, the fused single-launch kernel for small ones (latency-bound) — unless a
+// world does not fit the fused kernel's shared memory (a few worlds of many bodies), which also go to the staged
+// pipeline: xpbd_batch_create's bodies_per_world range is reachable for every n_worlds.
+static int forced_world_path() {  // 0 = no override, 1 = fused, 2 = staged
     const char* v = getenv("XPBD_WORLD_PATH");
-    bool staged = b->desc.n_worlds >= 4096;
-    if (v && !strcmp(v, "fused")) staged = false;
-    if (v && !strcmp(v, "staged")) staged = true;
-    return staged;
+    if (v && !strcmp(v, "fused")) return 1;
+    if (v && !strcmp(v, "staged")) return 2;
+    return 0;
+}
+bool world_path_is_staged(const xpbd_batch* b) {
+    const int forced = forced_world_path();
+    if (forced) return forced == 2;
+    return b->desc.n_worlds >= 4096 || b->fused_too_large;
 }
 int step_world(xpbd_batch* b, float frame_dt, int substeps, int n_frames) {
-    return world_path_is_staged(b) ? step_world_staged(b, frame_dt, substeps, n_frames) : step_world_fused(b, frame_dt, substeps, n_frames);
+    if (world_path_is_staged(b)) return step_world_staged(b, frame_dt, substeps, n_frames);
+    const int rc = step_world_fused(b, frame_dt, substeps, n_frames);
+    if (rc == XPBD_ERR_CAPACITY && !forced_world_path()) {
+        // the fused kernel's capacity checks run before anything is enqueued: nothing to undo
+        b->fused_too_large = true;
+        return step_world_staged(b, frame_dt, substeps, n_frames);
+    }
+    return rc;
 }
 }  // namespace xpbd
 
@@ -102,10 +115,10 @@ int xpbd_batch_create(const xpbd_batch_desc* desc, xpbd_batch** out) {
     b->arrays.dynA = take4(); b->arrays.dynB = take4(); b->arrays.dynC = take4(); b->arrays.dynD = take1();
     b->arrays.k0 = take4(); b->arrays.k1 = take4(); b->arrays.k2 = take4(); b->arrays.k3 = take4();
     b->arrays.k4 = take4(); b->arrays.k5 = take4(); b->arrays.k6 = take1();
-    TRY_OR_BAIL(cudaMalloc(&b->d_counters, 4 * sizeof(unsigned long long)));
-    TRY_OR_BAIL(cudaMemsetAsync(b->d_counters, 0, 4 * sizeof(unsigned long long), b->stream));
-    TRY_OR_BAIL(cudaMallocHost(&b->h_counters, 4 * sizeof(unsigned long long)));
-    std::memset(b->h_counters, 0, 4 * sizeof(unsigned long long));
+    TRY_OR_BAIL(cudaMalloc(&b->d_counters, kBatchCounters * sizeof(unsigned long long)));
+    TRY_OR_BAIL(cudaMemsetAsync(b->d_counters, 0, kBatchCounters * sizeof(unsigned long long), b->stream));
+    TRY_OR_BAIL(cudaMallocHost(&b->h_counters, kBatchCounters * sizeof(unsigned long long)));
+    std::memset(b->h_counters, 0, kBatchCounters * sizeof(unsigned long long));
     TRY_OR_BAIL(cudaEventCreate(&b->ev_start));
     TRY_OR_BAIL(cudaEventCreate(&b->ev_stop));
     for (int k = 0; k < 5; ++k) TRY_OR_BAIL(cudaEventCreate(&b->ev_stage[k]));
@@ -349,7 +362,7 @@ static int step_common(xpbd_batch* b, double dt, int32_t substep_count, int32_t 
     if (int rc = finalize_hulls(b)) return rc;
     if (in || out) { if (int rc = ensure_dyn_stage(b)) return rc; }
     XPBD_CUDA_TRY(cudaEventRecord(b->ev_start, b->stream));
-    XPBD_CUDA_TRY(cudaMemsetAsync(b->d_counters, 0, 4 * sizeof(unsigned long long), b->stream));
+    XPBD_CUDA_TRY(cudaMemsetAsync(b->d_counters, 0, kBatchCounters * sizeof(unsigned long long), b->stream));
     b->stage_timed = false;
     b->last.sub_batches = 1;
     const bool world_path = b->desc.body_body_contacts != 0 || b->desc.joints_per_world > 0;
@@ -372,7 +385,12 @@ static int step_common(xpbd_batch* b, double dt, int32_t substep_count, int32_t 
     b->io_in = nullptr;
     b->io_out = nullptr;
     if (b->last.sub_batches <= 1) b->fork_needed = true;  // this step's kernels ran on the batch stream itself
-    XPBD_CUDA_TRY(cudaMemcpyAsync(b->h_counters, b->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost,
+    // multi-body paths: count the worlds that went NaN / Inf (the single-body kernel counts in its epilogue)
+    if (world_path) {
+        launch_count_nan_worlds(b->arrays, b->desc.n_worlds, b->desc.bodies_per_world, b->d_counters + 4, b->stream);
+        b->last.kernel_launches += 1;
+    }
+    XPBD_CUDA_TRY(cudaMemcpyAsync(b->h_counters, b->d_counters, kBatchCounters * sizeof(unsigned long long), cudaMemcpyDeviceToHost,
                                   b->stream));
     XPBD_CUDA_TRY(cudaEventRecord(b->ev_stop, b->stream));
     b->last.body_substeps = (uint64_t)b->n_bodies * (uint64_t)substep_count * (uint64_t)n_frames;
@@ -401,6 +419,7 @@ int xpbd_batch_last_stats(xpbd_batch* b, xpbd_step_stats* out) {
     b->last.constraints = cnt[0];
     b->last.overflow_worlds = cnt[1];
     b->last.candidate_pairs = b->stage_timed ? cnt[3] : 0;
+    b->last.nan_worlds = (int32_t)std::min<unsigned long long>(b->h_counters[4], 0x7fffffffull);
     for (int k = 0; k < 4; ++k) {
         b->last.stage_ms[k] = 0.f;
         if (b->stage_timed) XPBD_CUDA_TRY(cudaEventElapsedTime(&b->last.stage_ms[k], b->ev_stage[k], b->ev_stage[k + 1]));

@@ -102,6 +102,25 @@ __global__ void hull_planes_kernel(uint32_t* blob, int n_hulls) {
     }
 }
 
+// Failure detection (the reference panics; here a diverged world is counted): worlds whose dynamic
+// state holds a NaN / Inf after a step call.  Thread per world over its B bodies; one atomic per warp that saw any.
+__global__ void count_nan_worlds_kernel(BodyArrays s, int64_t n_worlds, int B, unsigned long long* counter) {
+    const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool bad = false;
+    if (w < n_worlds) {
+        for (int b = 0; b < B; ++b) {
+            BodyDyn d;
+            load_dyn(s, w * B + b, d);
+            bad = bad || dyn_nonfinite(d);
+        }
+    }
+    const unsigned n = __popc(__ballot_sync(0xffffffffu, bad));
+    if ((threadIdx.x & 31) == 0 && n) atomicAdd(counter, (unsigned long long)n);
+}
+void launch_count_nan_worlds(const BodyArrays& s, int64_t n_worlds, int B, unsigned long long* counter, cudaStream_t st) {
+    if (n_worlds > 0) count_nan_worlds_kernel<<<(unsigned)((n_worlds + 127) / 128), 128, 0, st>>>(s, n_worlds, B, counter);
+}
+
 void launch_aos64_to_soa(const double* aos, const BodyArrays& s, int64_t first, int64_t n, cudaStream_t st) {
     if (n > 0) aos64_to_soa_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(aos, s, first, n);
 }

@@ -63,7 +63,9 @@ void launch_broadcast_world(const BodyArrays& s, int bodies_per_world, int64_t n
 void launch_dyn_pack(const BodyArrays& s, float* out, int64_t first, int64_t n, cudaStream_t st);
 void launch_dyn_unpack(const float* in, const BodyArrays& s, int64_t first, int64_t n, cudaStream_t st);
 void launch_hull_planes(uint32_t* blob, int n_hulls, cudaStream_t st);
+void launch_count_nan_worlds(const BodyArrays& s, int64_t n_worlds, int B, unsigned long long* counter, cudaStream_t st);
 
+constexpr int kBatchCounters = 8;
 struct SingleStepParams;
 struct WorldStepParams;
 
@@ -98,7 +100,7 @@ struct xpbd_batch {
     int64_t stage_bodies = 0;
     float* d_dyn_stage = nullptr;  // n_bodies x 13 floats, allocated on first use
     // stats
-    unsigned long long* d_counters = nullptr;  // [0] constraints, [1] overflow worlds, [2] tma fallbacks
+    unsigned long long* d_counters = nullptr;  // kBatchCounters: [0] constraints, [1] overflow worlds, [2] tma fallbacks, [3] candidates, [4] NaN worlds
     unsigned long long* h_counters = nullptr;  // pinned
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     cudaEvent_t ev_stage[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // staged pipeline: around the last substep's kernels
@@ -106,6 +108,7 @@ struct xpbd_batch {
     xpbd_step_stats last{};
     bool stepped = false;
     void* world_scratch = nullptr;  // owned by the multi-body path
+    bool fused_too_large = false;   // a world of this batch does not fit the fused kernel's shared memory: staged pipeline
     // single-body path: thread -> body permutation that groups bodies by their ground-contact count (xpbd_single.cu)
     int32_t* d_order[2] = {nullptr, nullptr};  // [cur] read by the step kernel, [cur ^ 1] written by the regrouping pass
     int order_cur = 0;

@@ -27,8 +27,17 @@ int step_bodies_once(xpbd_rigid* const* rigids, int n, const xpbd_polytope* hull
     if (rc == XPBD_OK) rc = xpbd_batch_upload(b, 0, n, host.data());
     if (rc == XPBD_OK) rc = xpbd_batch_step(b, dt, substeps, 1);
     if (rc == XPBD_OK) rc = xpbd_batch_download(b, 0, n, host.data());
-    if (rc == XPBD_OK)
-        for (int i = 0; i < n; ++i) *rigids[i] = host[(size_t)i];
+    if (rc == XPBD_OK) {
+        // solver::step only mutates velocity, angular_velocity, position and rotation (src/solver.rs:3-17): write back
+        // those 13 values (at fp32 precision) and leave the caller's f64 constants — inverse mass / inertia, forces,
+        // torques, centre of mass — untouched, so that a caller mixing this drop-in with its own f64 code keeps them.
+        for (int i = 0; i < n; ++i) {
+            const xpbd_rigid& h = host[(size_t)i];
+            xpbd_rigid& r = *rigids[i];
+            for (int k = 0; k < 3; ++k) { r.velocity[k] = h.velocity[k]; r.angular_velocity[k] = h.angular_velocity[k]; r.position[k] = h.position[k]; }
+            for (int k = 0; k < 4; ++k) r.rotation[k] = h.rotation[k];
+        }
+    }
     xpbd_batch_destroy(b);
     return rc;
 }

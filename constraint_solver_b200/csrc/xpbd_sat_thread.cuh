@@ -1,0 +1,213 @@
+// SAT stage, THREAD per candidate pair, for batches in which every hull is cube-shaped (8 vertices, 12 edges,
+// 6 faces: C3 / C5).  Included by xpbd_staged.cu after StagedParams.
+//
+// Same queries, same arithmetic per value as the warp-cooperative kernels (face_query_t / edge_query_culled_t in
+// xpbd_narrow.cuh; the reference's face_axes_separation / edge_axes_separation, src/collision.rs:123-197) — only the
+// schedule differs: one thread walks its candidate's 6 + 6 faces and 144 edge pairs serially, so the "first strict
+// maximum" of the reference's scans is a plain `>` and there are no shuffles, votes, ballots, queues or warp syncs.
+// The warp-per-two-candidates kernel spends 862 warp-instructions per candidate, i.e. 27.6 k thread slots, on 9.1 k
+// useful flops (profiles/r01j_stage_sat.txt); here the instruction stream of a thread is little more than the flops.
+//
+// Data placement per thread:
+//   registers     : the 16 world-space vertices of the two hulls (every support scan indexes them with compile-time
+//                   constants after unrolling), B's 12 edge vectors during the cull;
+//   shared memory : a per-thread copy of the 16 vertices as float4 [vertex][thread] (LDS.128, conflict-free for any
+//                   vertex index) for the accesses whose vertex index is hull data (edge end points, witnesses), and
+//                   the per-thread survivor masks of the cull, 12 bits per edge of A, [edge][thread].
+// No two threads share scratch, so the kernel has no barrier after the hull table is staged.
+#pragma once
+
+namespace xpbd {
+
+constexpr int kSatThreadBlock = 128;
+#ifndef XPBD_SAT_THREAD_MIN_BLOCKS
+#define XPBD_SAT_THREAD_MIN_BLOCKS 4
+#endif
+__host__ __device__ inline size_t sat_thread_smem_bytes(uint32_t hull_blob_bytes) {
+    return (size_t)hull_blob_bytes + (size_t)kSatThreadBlock * (16 * sizeof(float4) + 12 * sizeof(uint32_t));
+}
+
+// sqrt for the witness heuristic only (never feeds a result): one MUFU instead of the correctly rounded sequence
+XD float sqrt_approx(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+struct SatThreadScratch {
+    float4* W;      // [16][kSatThreadBlock], already offset by the thread index: A's vertices 0..7, B's 8..15
+    uint32_t* M;    // [12][kSatThreadBlock], offset by the thread index
+    XD V3 vert(int v) const { const float4 x = W[v * kSatThreadBlock]; return v3(x.x, x.y, x.z); }
+};
+
+// face_axes_separation (src/collision.rs:123-149) of a 6-face hull against 8 vertices `WO` of the other hull; L = those
+// vertices in the face hull's local space (kept by the caller for the witnesses).
+XD void face_query_thread(const float4* planes, const Fr& Finv, const V3 (&WO)[8], V3 (&L)[8], float& out_d, int& out_face) {
+#pragma unroll
+    for (int v = 0; v < 8; ++v) L[v] = Finv * WO[v];  // frames.0.inverse() * (frames.1 * p)
+    float best = -FLT_MAX;
+    int bi = -1;
+#pragma unroll 1
+    for (int f = 0; f < 6; ++f) {
+        const float4 pl = planes[f];
+        const V3 n = v3(pl.x, pl.y, pl.z);
+        float m = dot(n, L[0]);
+#pragma unroll
+        for (int v = 1; v < 8; ++v) m = fminf(m, dot(n, L[v]));
+        const float distance = fsub(m, pl.w);  // plane.distance(support)
+        if (distance > best) { best = distance; bi = f; }
+    }
+    out_d = best;
+    out_face = bi;
+}
+
+// The cull's two witnesses (see witness_vertices in xpbd_narrow.cuh): B's deepest vertex below the plane and a second deep
+// vertex far from the first.  Heuristic only — any two vertices of B are valid witnesses.
+XD int2 witness_vertices_thread(float4 plane, const V3 (&L)[8]) {
+    const V3 n = v3(plane.x, plane.y, plane.z);
+    float dep[8];
+    int v1 = 0;
+#pragma unroll
+    for (int v = 0; v < 8; ++v) dep[v] = dot(n, L[v]);
+    float d1 = dep[0];
+#pragma unroll
+    for (int v = 1; v < 8; ++v) if (dep[v] < d1) { d1 = dep[v]; v1 = v; }
+    V3 p1 = L[0];
+#pragma unroll
+    for (int v = 1; v < 8; ++v) if (v == v1) p1 = L[v];
+    int v2 = 0;
+    float k2 = FLT_MAX;
+#pragma unroll
+    for (int v = 0; v < 8; ++v) {
+        const V3 r = L[v] - p1;
+        const float k = dep[v] - 0.5f * sqrt_approx(r.x * r.x + r.y * r.y + r.z * r.z);
+        if (k < k2) { k2 = k; v2 = v; }
+    }
+    return make_int2(v1, v2);
+}
+
+template <bool kCull>
+XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, const SatThreadScratch& S) {
+    const int B = P.B, maxV = P.S.maxV;
+    const int64_t world = d.w;
+    const int64_t gi = world * B + (d.y & 0xffff), gj = world * B + (d.y >> 16);
+    const HullDesc& hA = T.desc(d.z & 0xffff);
+    const HullDesc& hB = T.desc(d.z >> 16);
+    float da, db = 0.f, de = 0.f;
+    int fa, fb = -1, ep = -1;
+    PairFeature pf; pf.feature = kNone; pf.index = -1;
+    uint32_t rkey = 0;
+    int2 wi = make_int2(0, 0);
+    V3 CA;
+    {
+        V3 WA[8], WB[8], L[8];
+#pragma unroll
+        for (int v = 0; v < 8; ++v) {
+            const float4 x = P.S.verts[gi * maxV + v], y = P.S.verts[gj * maxV + v];
+            WA[v] = v3(x.x, x.y, x.z); WB[v] = v3(y.x, y.y, y.z);
+            S.W[v * kSatThreadBlock] = x; S.W[(8 + v) * kSatThreadBlock] = y;
+            if (kCull) rkey = max(rkey, max(abs_coord_key(x), abs_coord_key(y)));
+        }
+        const float4 ra = P.bodies.dynC[gi], rb = P.bodies.dynC[gj];
+        const float4 fa4 = P.S.finvp[gi], fb4 = P.S.finvp[gj], ca4 = P.S.cen[gi];
+        CA = v3(ca4.x, ca4.y, ca4.z);
+        Fr finvA, finvB;
+        finvA.q = conjugate(q4(ra.w, ra.x, ra.y, ra.z)); finvA.p = v3(fa4.x, fa4.y, fa4.z);
+        finvB.q = conjugate(q4(rb.w, rb.x, rb.y, rb.z)); finvB.p = v3(fb4.x, fb4.y, fb4.z);
+        const float4* planesA = reinterpret_cast<const float4*>(T.words + hA.plane_off);
+        const float4* planesB = reinterpret_cast<const float4*>(T.words + hB.plane_off);
+        face_query_thread(planesA, finvA, WB, L, da, fa);
+        if (da >= 0.0f) goto done;
+        if (kCull) wi = witness_vertices_thread(planesA[fa < 0 ? 0 : fa], L);
+        face_query_thread(planesB, finvB, WA, L, db, fb);
+        if (db >= 0.0f) goto done;
+    }
+    {
+        const int2* EA = reinterpret_cast<const int2*>(T.words + hA.edge_off);
+        const int2* EB = reinterpret_cast<const int2*>(T.words + hB.edge_off);
+        // ---- stage 1 of the culled edge query (edge_query_culled_t): which of the 144 pairs can matter
+        if (kCull) {
+            const EdgeCull cull = make_edge_cull(da, db, __int_as_float((int)rkey), S.vert(8 + wi.x), S.vert(8 + wi.y));
+            const float tm = fabsf(cull.T) + cull.M;
+            const float K = tm * tm, Kf = cull.M * cull.M;
+            V3 eb[12];
+#pragma unroll
+            for (int jb = 0; jb < 12; ++jb) { const int2 e = EB[jb]; eb[jb] = S.vert(8 + e.y) - S.vert(8 + e.x); }
+#pragma unroll 1
+            for (int ia = 0; ia < 12; ++ia) {
+                const int2 ea = EA[ia];
+                const V3 foot = S.vert(ea.x);
+                const V3 edge_a = S.vert(ea.y) - foot;
+                uint32_t bits = 0;
+#pragma unroll
+                for (int jb = 0; jb < 12; ++jb) {
+                    const V3 c = cross(edge_a, eb[jb]);
+                    const float c2 = dot(c, c);
+                    const float df = dot(c, foot);
+                    const float f = df - dot(c, CA);
+                    const float u1 = dot(c, cull.w1) - df, u2 = dot(c, cull.w2) - df;
+                    const float us = f < 0.0f ? -fmaxf(u1, u2) : fminf(u1, u2);  // the smaller of the two bounds, flipped like the axis
+                    const bool below = us < 0.0f && fmul(us, us) > fmul(K, c2) && fmul(f, f) > fmul(Kf, c2) && c2 > 1e-24f;
+                    const bool keep = !below && c2 > 0.0f;
+                    bits |= (keep ? 1u : 0u) << jb;
+                }
+                S.M[ia * kSatThreadBlock] = bits;
+            }
+        }
+        // ---- stage 2: the reference's arithmetic (src/collision.rs:166-193) for the surviving pairs, in scan order
+        V3 XA[8], XB[8];
+#pragma unroll
+        for (int v = 0; v < 8; ++v) { XA[v] = S.vert(v); XB[v] = S.vert(8 + v); }
+        float best = -FLT_MAX;
+        int bi = -1;
+#pragma unroll 1
+        for (int ia = 0; ia < 12; ++ia) {
+            uint32_t bits = kCull ? S.M[ia * kSatThreadBlock] : 0xfffu;
+            if (!bits) continue;
+            const int2 ea = EA[ia];
+            const V3 foot = S.vert(ea.x);
+            const V3 edge_a = S.vert(ea.y) - foot;
+            const V3 fc = foot - CA;
+            while (bits) {
+                const int jb = __ffs((int)bits) - 1;
+                bits &= bits - 1;
+                const int2 e = EB[jb];
+                const V3 edge_b = S.vert(8 + e.y) - S.vert(8 + e.x);
+                V3 axis = normalize(cross(edge_a, edge_b));  // parallel edges -> NaN axis, no guard (as the reference)
+                if (dot(axis, fc) < 0.0f) axis = -axis;
+                // Ignore if another point on `a` is further in the direction to `b`.
+                float sa = dot(axis, XA[0]);
+#pragma unroll
+                for (int v = 1; v < 8; ++v) sa = fmaxf(sa, dot(axis, XA[v]));
+                if (sa > dot(foot, axis)) continue;
+                const float disp = plane_displacement(foot, axis);
+                float sb = dot(axis, XB[0]);
+#pragma unroll
+                for (int v = 1; v < 8; ++v) sb = fminf(sb, dot(axis, XB[v]));
+                const float distance = fsub(sb, disp);
+                if (distance > best) { best = distance; bi = ia * 12 + jb; }  // serial scan: strict > keeps the first maximum
+            }
+        }
+        de = best; ep = bi;
+        if (!(de >= 0.0f)) pf = choose_feature(da, fa, db, fb, de, ep);
+    }
+done:
+    P.S.pairs[d.x].y = pf.feature;
+    P.S.pairs[d.x].z = pf.index;
+}
+
+template <bool kCull>
+__global__ void __launch_bounds__(kSatThreadBlock, XPBD_SAT_THREAD_MIN_BLOCKS) stage_sat_thread_kernel(StagedParams P) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    __shared__ __align__(8) uint64_t bar;
+    stage_bulk(smem, P.hull_blob, P.hull_blob_bytes, &bar, reinterpret_cast<unsigned int*>(P.counters + 2));
+    const HullTable T{smem};
+    SatThreadScratch S;
+    S.W = reinterpret_cast<float4*>(smem + P.hull_blob_bytes / 4) + threadIdx.x;
+    S.M = reinterpret_cast<uint32_t*>(reinterpret_cast<float4*>(smem + P.hull_blob_bytes / 4) + 16 * kSatThreadBlock) + threadIdx.x;
+    const unsigned count = *P.S.work_count;
+    for (unsigned it = blockIdx.x * blockDim.x + threadIdx.x; it < count; it += gridDim.x * blockDim.x)
+        sat_thread_candidate<kCull>(P, T, P.S.worklist[it], S);
+}
+
+}  // namespace xpbd

@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(128) step_single_kernel(SingleStepParams P) {
 
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     unsigned int applied = 0;
+    bool bad = false;  // this body's state is NaN / Inf after the call (xpbd_step_stats.nan_worlds; a world = one body here)
     if (t < P.n_bodies) {
         const int64_t g = P.order ? P.order[t] : t;
         unsigned int last = 0;
@@ -108,11 +109,14 @@ __global__ void __launch_bounds__(128) step_single_kernel(SingleStepParams P) {
             rigid_derive(d, past_position, past_rotation, sc.dt);
         }
         store_dyn(P.bodies, g, d);
+        bad = dyn_nonfinite(d);
         if (P.contact_count) P.contact_count[g] = (uint8_t)(last < 15u ? last : 15u);
     }
     // one atomic per warp
     for (int o = 16; o > 0; o >>= 1) applied += __shfl_down_sync(0xffffffffu, applied, o);
     if ((threadIdx.x & 31) == 0 && applied) atomicAdd(P.constraint_counter, (unsigned long long)applied);
+    const unsigned nbad = __popc(__ballot_sync(0xffffffffu, bad));
+    if ((threadIdx.x & 31) == 0 && nbad) atomicAdd(P.constraint_counter + 4, (unsigned long long)nbad);
 }
 
 // ---- regrouping: bodies with the same number of ground contacts share warps --------------------------------------------

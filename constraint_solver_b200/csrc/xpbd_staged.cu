@@ -17,7 +17,9 @@
 // influence results because every candidate writes into its own (world, pair) slot).  Per substep the extra HBM/L2
 // traffic is ~5 KB per world — about 1 % of the measured HBM bandwidth at the achieved rate.
 #include <cstdlib>
+#include <cstring>
 
+#include "xpbd_host_math.hpp"
 #include "xpbd_internal.hpp"
 #include "xpbd_narrow.cuh"
 #include "xpbd_rigid.cuh"
@@ -455,6 +457,10 @@ __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_cubes_kern
     }
 }
 
+}  // namespace xpbd
+#include "xpbd_sat_thread.cuh"  // stage_sat_thread_kernel: thread per candidate (cube-shaped hulls)
+namespace xpbd {
+
 // ---- stage 3: manifolds (thread per candidate pair) -> fresh contacts in the pair's slot --------------------
 #ifndef XPBD_MANIFOLD_MIN_BLOCKS
 #define XPBD_MANIFOLD_MIN_BLOCKS 4
@@ -727,6 +733,8 @@ struct StagedState {
     int B = 0;
     int grid_prepare = 0, grid_sat = 0, grid_manifold = 0;
     size_t smem_prepare = 0, smem_sat = 0, smem_manifold = 0;
+    int sat_threads = 256;        // block size of sat_fn
+    int sat_cands_per_block = 8;  // candidates one block of sat_fn takes per grid-stride round
     int warps_prepare = 8;
     int clip_cap = kMaxClip;
     void (*manifold_fn)(StagedParams) = nullptr;
@@ -757,14 +765,16 @@ struct StagedState {
 constexpr int kWorkCountStride = 32;  // uint32 words between the work counters of two sub-batches (own 128-byte line each)
 constexpr int kMaxSubBatches = 8;
 
-void release_world_scratch(xpbd_batch* b) {
-    if (!b->world_scratch) return;
-    StagedState* st = static_cast<StagedState*>(b->world_scratch);
+static void destroy_staged(StagedState* st) {
     st->buf.release();
     st->release_streams();
     if (st->d_range_counters) cudaFree(st->d_range_counters);
     if (st->h_range_counters) cudaFreeHost(st->h_range_counters);
     delete st;
+}
+void release_world_scratch(xpbd_batch* b) {
+    if (!b->world_scratch) return;
+    destroy_staged(static_cast<StagedState*>(b->world_scratch));
     b->world_scratch = nullptr;
 }
 
@@ -775,14 +785,22 @@ static cudaError_t dev_alloc(T*& p, size_t n, size_t& total) {
     return cudaMalloc(reinterpret_cast<void**>(&p), bytes > 16 ? bytes : 16);
 }
 
+static int build_staged(xpbd_batch* b, StagedState* st);
+// The state is published in b->world_scratch only once it is complete: a failed allocation / capacity check leaves no
+// half-built cache behind (the next step call starts over and reports the original error again).
 static int ensure_staged(xpbd_batch* b, StagedState*& out) {
-    const int B = b->desc.bodies_per_world;
-    const DeviceHulls& H = b->dev_hulls;
     StagedState* st = static_cast<StagedState*>(b->world_scratch);
-    if (st && st->buf.maxV == H.max_verts && st->n_hulls == b->hulls.size()) { out = st; return XPBD_OK; }
+    if (st && st->buf.maxV == b->dev_hulls.max_verts && st->n_hulls == b->hulls.size()) { out = st; return XPBD_OK; }
     release_world_scratch(b);
     st = new StagedState();
+    if (int rc = build_staged(b, st)) { destroy_staged(st); return rc; }
     b->world_scratch = st;
+    out = st;
+    return XPBD_OK;
+}
+static int build_staged(xpbd_batch* b, StagedState* st) {
+    const int B = b->desc.bodies_per_world;
+    const DeviceHulls& H = b->dev_hulls;
     st->n_worlds = b->desc.n_worlds;
     st->B = B;
     st->n_hulls = b->hulls.size();
@@ -846,8 +864,23 @@ static int ensure_staged(xpbd_batch* b, StagedState*& out) {
             for (size_t f = 0; quads && f + 1 < h.face_offsets.size(); ++f) quads = h.face_offsets[f + 1] - h.face_offsets[f] == 4;
             all_cubes = all_cubes && h.vertices.size() == 8 * 3 && h.edges.size() == 12 * 2 && quads;
         }
-        const char* e = std::getenv("XPBD_SAT_DUAL");
-        if (all_cubes && !(e && e[0] == '0')) st->sat_fn = cull ? stage_sat_cubes_kernel<true> : stage_sat_cubes_kernel<false>;
+        // Schedules of the SAT stage for all-cube batches (XPBD_SAT_SCHED, A/B runs): "thread" (default) = thread per
+        // candidate, "dual" = two candidates per warp, "warp" = the generic warp-per-candidate kernel.
+        const char* e = std::getenv("XPBD_SAT_SCHED");
+        const char* dual = std::getenv("XPBD_SAT_DUAL");
+        const bool want_warp = (e && !std::strcmp(e, "warp")) || (dual && dual[0] == '0');
+        const bool want_dual = e && !std::strcmp(e, "dual");
+        if (all_cubes && !want_warp) {
+            if (want_dual) {
+                st->sat_fn = cull ? stage_sat_cubes_kernel<true> : stage_sat_cubes_kernel<false>;
+                st->sat_cands_per_block = 16;
+            } else {
+                st->sat_fn = cull ? stage_sat_thread_kernel<true> : stage_sat_thread_kernel<false>;
+                st->sat_threads = kSatThreadBlock;
+                st->sat_cands_per_block = kSatThreadBlock;
+                st->smem_sat = sat_thread_smem_bytes(H.bytes);
+            }
+        }
     }
     XPBD_CUDA_TRY(cudaFuncSetAttribute(st->sat_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem_sat));
     st->manifold_fn = st->clip_cap == 8 ? stage_manifold_kernel<8> : stage_manifold_kernel<kMaxClip>;
@@ -855,11 +888,10 @@ static int ensure_staged(xpbd_batch* b, StagedState*& out) {
     int occ = 1;
     XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, st->prepare_fn, 32 * wp, st->smem_prepare));
     st->occ_prepare = occ > 0 ? occ : 1;
-    XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, st->sat_fn, 256, st->smem_sat));
+    XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, st->sat_fn, st->sat_threads, st->smem_sat));
     st->occ_sat = occ > 0 ? occ : 1;
     XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, st->manifold_fn, kManifoldThreads, st->smem_manifold));
     st->occ_manifold = occ > 0 ? occ : 1;
-    out = st;
     return XPBD_OK;
 }
 
@@ -947,7 +979,8 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
     if (int rc = ensure_sub_streams(b, st, n_sub)) return rc;
     // Resident blocks per SM of the persistent SAT kernel: everything the registers allow when it runs alone, 2 when
     // several ranges share the device (measured on C3 with 4 ranges: 2 -> 6.47e8, 3 -> 6.42e8, 4 -> 6.33e8 body-substeps/s).
-    int occ_sat = n_sub > 1 ? std::min(st->occ_sat, 2) : st->occ_sat;
+    // (the thread-per-candidate kernel has 128-thread blocks: the same 16 warps are 4 of them)
+    int occ_sat = n_sub > 1 ? std::min(st->occ_sat, std::max(2, 512 / st->sat_threads)) : st->occ_sat;
     if (const char* e = std::getenv("XPBD_SAT_BLOCKS_PER_SM")) occ_sat = std::min(st->occ_sat, std::max(1, std::atoi(e)));
     const int total = substeps * n_frames;
     // The ranges wait for the batch stream only when something was enqueued there since the last step call
@@ -989,7 +1022,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
         }
         XPBD_CUDA_TRY(cudaMemsetAsync(S.overflow, 0, (size_t)nw * sizeof(int), stream));
         const int grid_prepare = (int)std::min<int64_t>((nw + worlds_per_block - 1) / worlds_per_block, (int64_t)st->n_sm * st->occ_prepare);
-        const int grid_sat = (int)std::min<int64_t>((nw * S.capP + 7) / 8, (int64_t)st->n_sm * occ_sat);
+        const int grid_sat = (int)std::min<int64_t>((nw * S.capP + st->sat_cands_per_block - 1) / st->sat_cands_per_block, (int64_t)st->n_sm * occ_sat);
         const int grid_manifold = (int)std::min<int64_t>((nw * S.capP + 127) / 128, (int64_t)st->n_sm * st->occ_manifold);
         unsigned grid_solve = (unsigned)((2 * nw + 127) / 128);
         if (st->solve_blocks_per_sm > 0) grid_solve = std::min(grid_solve, (unsigned)(st->solve_blocks_per_sm * st->n_sm));
@@ -1000,7 +1033,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
             if (timed) cudaEventRecord(b->ev_stage[0], stream);
             st->prepare_fn<<<grid_prepare, 32 * st->warps_prepare, st->smem_prepare, stream>>>(Q);
             if (timed) cudaEventRecord(b->ev_stage[1], stream);
-            if (P.body_body) st->sat_fn<<<grid_sat, 256, st->smem_sat, stream>>>(Q);
+            if (P.body_body) st->sat_fn<<<grid_sat, st->sat_threads, st->smem_sat, stream>>>(Q);
             if (timed) cudaEventRecord(b->ev_stage[2], stream);
             if (P.body_body) st->manifold_fn<<<grid_manifold, kManifoldThreads, st->smem_manifold, stream>>>(Q);
             if (timed) cudaEventRecord(b->ev_stage[3], stream);
@@ -1027,3 +1060,105 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
 }
 
 }  // namespace xpbd
+
+// ---- the SAT stage on synthetic candidates (A/B testing of its schedules and of the witness cull) -------------------
+namespace xpbd {
+// One "world" per candidate: bodies 2i (A) and 2i + 1 (B), pair slot i.  Fills exactly what stage_prepare leaves behind
+// for the SAT stage: world-space vertices (frame * vertex, the same expression), inverse frame positions, A's world
+// centroid, the rotations, the pair record and the work-list descriptor.
+__global__ void sat_fuzz_setup_kernel(const double* fa, const double* fb, int64_t n, const uint32_t* hull_blob, int maxV,
+                                      float4* dynC, float4* finvp, float4* cen, float4* verts, int4* pairs, int4* worklist,
+                                      int hull_b) {
+    const HullTable T{hull_blob};
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < 2 * n; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t >> 1;
+        const int side = (int)(t & 1);
+        const double* f = (side ? fb : fa) + 7 * i;
+        Fr frame;
+        frame.p = v3((float)f[0], (float)f[1], (float)f[2]);
+        frame.q = q4((float)f[6], (float)f[3], (float)f[4], (float)f[5]);
+        const HullDesc& hd = T.desc(side ? hull_b : 0);
+        const Fr finv = frame_inverse(frame);
+        const V3 c = frame * T.centroid(hd);
+        dynC[t] = make_float4(frame.q.x, frame.q.y, frame.q.z, frame.q.s);
+        finvp[t] = make_float4(finv.p.x, finv.p.y, finv.p.z, 0.f);
+        cen[t] = make_float4(c.x, c.y, c.z, 0.f);
+        for (int v = 0; v < hd.n_verts; ++v) {
+            const V3 p = frame * T.vertex(hd, v);
+            verts[t * maxV + v] = make_float4(p.x, p.y, p.z, 0.f);
+        }
+        if (!side) {
+            pairs[i] = make_int4(0 | (1 << 16), kNone, -1, 0);
+            worklist[i] = make_int4((int)i, 0 | (1 << 16), 0 | (hull_b << 16), (int)i);
+        }
+    }
+}
+}  // namespace xpbd
+
+extern "C" int xpbd_sat_feature_batch(const xpbd_frame* fa, const xpbd_frame* fb, int64_t n, const xpbd_polytope* ha,
+                                      const xpbd_polytope* hb, int32_t schedule, int32_t cull, int32_t* feature, int32_t* index) {
+    using namespace xpbd;
+    if (!fa || !fb || !ha || !hb || !feature || !index || n < 0) return fail(XPBD_ERR_INVALID, "bad argument");
+    if (schedule < 0 || schedule > 2) return fail(XPBD_ERR_INVALID, "schedule must be 0 (warp), 1 (two per warp) or 2 (thread)");
+    if (n >= (1ll << 30)) return fail(XPBD_ERR_CAPACITY, "at most 2^30 candidates per call");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(XPBD_ERR_CUDA, "no CUDA device; this library has no CPU fallback");
+    std::vector<HostHull> hulls;
+    for (const xpbd_polytope* h : {ha, hb}) {
+        if (const char* why = xpbd_host::validate_hull(h)) return fail(XPBD_ERR_INVALID, "hull: %s", why);
+        if (h->n_vertices > 64 || h->n_edges <= 0) return fail(XPBD_ERR_CAPACITY, "hulls need edges and at most 64 vertices");
+        hulls.push_back(copy_hull(h));
+        if (schedule != 0 && !(h->n_vertices == 8 && h->n_edges == 12 && h->n_faces == 6))
+            return fail(XPBD_ERR_INVALID, "schedules 1 and 2 are for cube-shaped hulls (8 vertices, 12 edges, 6 faces)");
+    }
+    DeviceHulls dev;
+    if (int rc = dev.upload(hulls, nullptr)) return rc;
+    struct Bufs {
+        DeviceHulls& dev;
+        std::vector<void*> ptrs;
+        ~Bufs() { for (void* p : ptrs) cudaFree(p); dev.release(); }
+        cudaError_t alloc(void** p, size_t bytes) { cudaError_t e = cudaMalloc(p, bytes ? bytes : 16); if (e == cudaSuccess) ptrs.push_back(*p); return e; }
+    } bufs{dev, {}};
+    if (n == 0) return XPBD_OK;
+    const int maxV = dev.max_verts;
+    double *d_fa, *d_fb;
+    StagedParams P{};
+    unsigned long long* d_counters;
+    XPBD_CUDA_TRY(bufs.alloc((void**)&d_fa, (size_t)n * 56)); XPBD_CUDA_TRY(bufs.alloc((void**)&d_fb, (size_t)n * 56));
+    XPBD_CUDA_TRY(bufs.alloc((void**)&P.bodies.dynC, (size_t)2 * n * 16));
+    XPBD_CUDA_TRY(bufs.alloc((void**)&P.S.finvp, (size_t)2 * n * 16)); XPBD_CUDA_TRY(bufs.alloc((void**)&P.S.cen, (size_t)2 * n * 16));
+    XPBD_CUDA_TRY(bufs.alloc((void**)&P.S.verts, (size_t)2 * n * maxV * 16));
+    XPBD_CUDA_TRY(bufs.alloc((void**)&P.S.pairs, (size_t)n * 16)); XPBD_CUDA_TRY(bufs.alloc((void**)&P.S.worklist, (size_t)n * 16));
+    XPBD_CUDA_TRY(bufs.alloc((void**)&P.S.work_count, 64)); XPBD_CUDA_TRY(bufs.alloc((void**)&d_counters, 32));
+    XPBD_CUDA_TRY(cudaMemcpy(d_fa, fa, (size_t)n * 56, cudaMemcpyHostToDevice));
+    XPBD_CUDA_TRY(cudaMemcpy(d_fb, fb, (size_t)n * 56, cudaMemcpyHostToDevice));
+    XPBD_CUDA_TRY(cudaMemset(d_counters, 0, 32));
+    const uint32_t wc[4] = {(uint32_t)n, 0, 0, 0};
+    XPBD_CUDA_TRY(cudaMemcpy(P.S.work_count, wc, sizeof wc, cudaMemcpyHostToDevice));
+    sat_fuzz_setup_kernel<<<1184, 256>>>(d_fa, d_fb, n, dev.blob, maxV, P.bodies.dynC, P.S.finvp, P.S.cen, P.S.verts, P.S.pairs,
+                                         P.S.worklist, 1);
+    XPBD_CUDA_TRY(cudaGetLastError());
+    P.n_worlds = n; P.B = 2; P.J = 0;
+    P.hull_blob = dev.blob; P.hull_blob_bytes = dev.bytes;
+    P.S.maxV = maxV; P.S.capP = 1;
+    P.body_body = 1;
+    P.counters = d_counters;
+    void (*fn)(StagedParams) = nullptr;
+    int threads = 256;
+    size_t smem = dev.bytes + 8 * (size_t)sat_words_per_warp(maxV) * 4;
+    if (schedule == 0) fn = cull ? stage_sat_kernel<true> : stage_sat_kernel<false>;
+    else if (schedule == 1) fn = cull ? stage_sat_cubes_kernel<true> : stage_sat_cubes_kernel<false>;
+    else { fn = cull ? stage_sat_thread_kernel<true> : stage_sat_thread_kernel<false>; threads = kSatThreadBlock; smem = sat_thread_smem_bytes(dev.bytes); }
+    XPBD_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 1, n_sm = 148, devid = 0;
+    XPBD_CUDA_TRY(cudaGetDevice(&devid));
+    XPBD_CUDA_TRY(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, devid));
+    XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, threads, smem));
+    fn<<<n_sm * (occ > 0 ? occ : 1), threads, smem>>>(P);
+    XPBD_CUDA_TRY(cudaGetLastError());
+    XPBD_CUDA_TRY(cudaDeviceSynchronize());
+    std::vector<int4> host((size_t)n);
+    XPBD_CUDA_TRY(cudaMemcpy(host.data(), P.S.pairs, (size_t)n * 16, cudaMemcpyDeviceToHost));
+    for (int64_t i = 0; i < n; ++i) { feature[i] = host[(size_t)i].y; index[i] = host[(size_t)i].z; }
+    return XPBD_OK;
+}

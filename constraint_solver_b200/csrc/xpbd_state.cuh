@@ -47,6 +47,15 @@ XD void store_dyn(const BodyArrays& s, int64_t g, const BodyDyn& d) {
     s.dynC[g] = make_float4(d.rotation.x, d.rotation.y, d.rotation.z, d.rotation.s);
     s.dynD[g] = d.angular_velocity.z;
 }
+// true when any of the 13 dynamic values is NaN or +-Inf (x * 0 is 0 for finite x and NaN otherwise)
+XD bool dyn_nonfinite(const BodyDyn& d) {
+    float s = fmul(d.position.x, 0.0f);
+    s = fadd(s, fmul(d.position.y, 0.0f)); s = fadd(s, fmul(d.position.z, 0.0f));
+    s = fadd(s, fmul(d.rotation.x, 0.0f)); s = fadd(s, fmul(d.rotation.y, 0.0f)); s = fadd(s, fmul(d.rotation.z, 0.0f)); s = fadd(s, fmul(d.rotation.s, 0.0f));
+    s = fadd(s, fmul(d.velocity.x, 0.0f)); s = fadd(s, fmul(d.velocity.y, 0.0f)); s = fadd(s, fmul(d.velocity.z, 0.0f));
+    s = fadd(s, fmul(d.angular_velocity.x, 0.0f)); s = fadd(s, fmul(d.angular_velocity.y, 0.0f)); s = fadd(s, fmul(d.angular_velocity.z, 0.0f));
+    return s != s;
+}
 XD void load_const(const BodyArrays& s, int64_t g, BodyConst& k) {
     float4 a = __ldg(&s.k0[g]), b = __ldg(&s.k1[g]), c = __ldg(&s.k2[g]), d = __ldg(&s.k3[g]);
     float4 e = __ldg(&s.k4[g]), f = __ldg(&s.k5[g]);

@@ -123,7 +123,8 @@ typedef struct xpbd_step_stats {
     float stage_ms[4];
     uint64_t candidate_pairs;
     int32_t sub_batches;        /* world ranges the last step call ran concurrently (see xpbd_batch_set_sub_batches) */
-    int32_t reserved;
+    int32_t nan_worlds;         /* worlds whose state holds a NaN / Inf after the last step call (the reference panics or
+                                 * silently propagates; here the world is isolated — neighbours are unaffected — and counted) */
 } xpbd_step_stats;
 
 /* ---- library / device ---------------------------------------------------------------- */
@@ -230,6 +231,16 @@ int xpbd_edge_axes_separation_batch(const xpbd_frame* frames_a, const xpbd_frame
 int xpbd_sat_manifold_batch(const xpbd_frame* frames_a, const xpbd_frame* frames_b, int64_t n,
                             const xpbd_polytope* hull_a, const xpbd_polytope* hull_b, xpbd_constraint* out,
                             int32_t* counts, int32_t* feature);
+
+/* The SAT stage of the multi-body step (the three queries + feature choice, without the manifold) on n synthetic
+ * candidate pairs, through the step's own kernels: schedule 0 = warp per candidate (any hulls), 1 = two candidates per
+ * warp, 2 = thread per candidate (1, 2: cube-shaped hulls, 8 vertices / 12 edges / 6 faces); cull 0 = the reference's
+ * full edge-pair scan (src/collision.rs:151-197), 1 = with the witness cull.  feature[i] as above, index[i] = face
+ * index or flat edge pair index ia * n_edges_b + jb (-1 when separated).  Every (schedule, cull) combination must
+ * return the same values: this is the A/B harness for that claim (tests/test_sat_fuzz.py). */
+int xpbd_sat_feature_batch(const xpbd_frame* frames_a, const xpbd_frame* frames_b, int64_t n,
+                           const xpbd_polytope* hull_a, const xpbd_polytope* hull_b, int32_t schedule, int32_t cull,
+                           int32_t* feature, int32_t* index);
 
 /* FP32 issue-rate microbenchmark (non-FMA FADD/FMUL chain) for the roofline denominator.
  * Returns achieved TFLOP/s on `device`. */

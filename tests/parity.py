@@ -23,3 +23,12 @@ def compare(gpu_rec: np.ndarray, cpu38_f32: np.ndarray):
     pos = np.abs(g[:, 31:34] - c[:, 31:34]).max() if len(g) else 0.0
     rot = rot_error(g[:, 34:38], c[:, 34:38]).max() if len(g) else 0.0
     return float(pos), float(rot), bool(np.array_equal(g, c))
+
+
+def compare_arrays(gpu38_f64: np.ndarray, cpu38_f32: np.ndarray):
+    """The same for an already flattened (n, 38) GPU array."""
+    g = gpu38_f64.reshape(-1, 38)
+    c = cpu38_f32.astype(np.float64).reshape(-1, 38)
+    pos = np.abs(g[:, 31:34] - c[:, 31:34]).max() if len(g) else 0.0
+    rot = rot_error(g[:, 34:38], c[:, 34:38]).max() if len(g) else 0.0
+    return float(pos), float(rot), bool(np.array_equal(g, c))

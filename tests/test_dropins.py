@@ -17,17 +17,29 @@ def _oracle_body(rec, hull_vertices, frames, substeps=25):
     return r.astype(np.float64)
 
 
+DYN = np.r_[22:28, 31:38]   # velocity, angular_velocity, position, rotation
+CONST = np.r_[0:22, 28:31]  # inverse mass / inertia, forces, torques, centre of mass
+
+
+def _same_dynamic_state_constants_untouched(rec, rec0, oracle38):
+    """The drop-ins write back what solver::step mutates (fp32 values, exact in f64) and leave the caller's f64
+    constants as they were (they used to come back fp32-rounded)."""
+    got, orig = xo.rigid38(np.array([rec]))[0], xo.rigid38(np.array([rec0]))[0]
+    return np.array_equal(got[DYN], oracle38.reshape(-1)[DYN]) and np.array_equal(got[CONST], orig[CONST])
+
+
 def test_solver_step_matches_oracle_frame_by_frame():
     """solver::step(&mut rigid, &polytope, dt, substep_count) (src/solver.rs:3), called the way app.rs does."""
     cube = cs.Polytope.new_cube()
     w = scenes.default_world()
     rigid = w.a.copy()
+    rec0 = rigid.rec.copy()
     ref = xo.rigid38(np.array([rigid.rec])).astype(np.float32)
     for _ in range(40):
         solver.step(rigid, cube, DT, 25)
         xo.step_bodies(ref, cube.vertices, DT, 25, 1, threads=1)
         # the one-shot call round-trips through f64 host records every frame; fp32 values survive that exactly
-        assert np.array_equal(xo.rigid38(np.array([rigid.rec])), ref.astype(np.float64))
+        assert _same_dynamic_state_constants_untouched(rigid.rec, rec0, ref.astype(np.float64))
 
 
 def test_world_integrate_steps_both_bodies_against_p1():
@@ -38,9 +50,12 @@ def test_world_integrate_steps_both_bodies_against_p1():
     frames = 100  # b is thrown upwards and lands after ~64 frames; only then does the hull matter
     for _ in range(frames):
         w.integrate(DT, p1, p2, None)
-    assert np.array_equal(xo.rigid38(np.array([w.a.rec])), _oracle_body(a0, p1.vertices, frames))
-    assert np.array_equal(xo.rigid38(np.array([w.b.rec])), _oracle_body(b0, p1.vertices, frames))
-    assert not np.array_equal(xo.rigid38(np.array([w.b.rec])), _oracle_body(b0, p2.vertices, frames))
+    assert _same_dynamic_state_constants_untouched(w.a.rec, a0, _oracle_body(a0, p1.vertices, frames))
+    assert _same_dynamic_state_constants_untouched(w.b.rec, b0, _oracle_body(b0, p1.vertices, frames))
+    assert not _same_dynamic_state_constants_untouched(w.b.rec, b0, _oracle_body(b0, p2.vertices, frames))
+    # b's inverse inertia (537.6 / -76.8, src/world.rs:27) is not fp32-exact: it must still be the caller's f64 value
+    assert np.array_equal(w.b.rec["inverse_inertia"], b0["inverse_inertia"]) and \
+        not np.array_equal(b0["inverse_inertia"], b0["inverse_inertia"].astype(np.float32).astype(np.float64))
 
 
 def test_one_shot_calls_validate_arguments():

@@ -120,7 +120,7 @@ def test_c2_full_size_properties_and_sampled_parity():
     with cs.Worlds(n) as w:
         w.add_hull(CUBE); w.upload(init); w.integrate(DT, 25, frames)
         out = w.download()
-        assert w.stats()["body_substeps"] == n * 25 * frames
+        assert w.stats()["body_substeps"] == n * 25 * frames and w.stats()["nan_worlds"] == 0
     g = xo.rigid38(out)
     assert np.isfinite(g).all()
     assert np.array_equal(g[0::2], g[1::2])
@@ -159,6 +159,7 @@ def test_nan_world_does_not_poison_neighbours():
     cpu, _ = _oracle(init, 20)
     with cs.Worlds(n) as w:
         w.add_hull(CUBE); w.upload(init); w.integrate(DT, 25, 20)
+        assert w.stats()["nan_worlds"] == 1  # failure detection: the caller learns it without downloading the state
         g = xo.rigid38(w.download())
     ok = np.arange(n) != 5
     assert np.array_equal(g[ok], cpu.astype(np.float64)[ok])

@@ -280,25 +280,90 @@ def test_sub_batches_stats_sum_over_ranges(world_path):
             w.integrate(DT, 20, 15)
             st = w.stats()
             res.append((st["constraints"], st["candidate_pairs"], st["overflow_worlds"]))
-            assert st["sub_batches"] == k and st["kernel_launches"] == k * 4 * 20 * 15
+            assert st["sub_batches"] == k and st["kernel_launches"] == k * 4 * 20 * 15 + 1  # + the NaN-world count
     assert res[0] == res[1] and res[0][1] > 0
 
 
-def test_c3_full_size_properties_and_sampled_parity():
-    """C3 at BASELINE size (100k worlds x 10 cubes): duplicated worlds give identical results, no NaN, no
-    overflow, stacks stay stacks; a sample of worlds is compared with the oracle."""
+def test_nan_worlds_are_counted_and_isolated(world_path):
+    """xpbd_step_stats.nan_worlds (failure detection): worlds 3 and 40 start with a NaN / Inf; they are
+    counted, and every other world still matches the oracle bit for bit."""
+    n = 64
+    init = scenes.c3_stack(n)
+    init["position"][3, 4, 1] = np.nan
+    init["velocity"][40, 0, 2] = np.inf
+    with cs.Worlds(n, 10, body_body_contacts=True) as w:
+        w.add_hull(CUBE); w.upload(init)
+        w.integrate(DT, 20, 5)
+        st = w.stats()
+        got = xo.rigid38(w.download()).reshape(n, 10, 38)
+    assert st["nan_worlds"] == 2, st
+    init_ok = init.copy()
+    init_ok[3], init_ok[40] = init_ok[0], init_ok[0]
+    cpu, _ = _run_cpu(init_ok, [CUBE], 5, 20)
+    ok = np.ones(n, dtype=bool); ok[[3, 40]] = False
+    assert np.array_equal(got[ok], cpu.astype(np.float64).reshape(n, 10, 38)[ok])
+
+
+def test_default_selector_small_batch_of_large_worlds(monkeypatch):
+    """with XPBD_WORLD_PATH unset, a few worlds of many bodies (125 per world do not fit the fused
+    kernel's shared memory) must fall back to the staged pipeline instead of failing with XPBD_ERR_CAPACITY."""
+    monkeypatch.delenv("XPBD_WORLD_PATH", raising=False)
+    init, hulls, ids, joints = scenes.c4_pile(3, n_side=5, spacing=1.5)
+    gpu, gcons = _run_gpu(init, hulls, 6, 20, hull_ids=ids, joints=joints)
+    cpu, c = _run_cpu(init, hulls, 6, 20, hull_ids=ids, joints=joints)
+    assert parity.compare(gpu, cpu)[2] and gcons == c["constraints"]
+
+
+def _sample_blocks(n, n_blocks, block):
+    """Sampled worlds: n_blocks contiguous blocks of `block` worlds spread over [0, n) — first and last worlds, and
+    (with 4 automatic world ranges) blocks on both sides of every range boundary are among them."""
+    starts = np.linspace(0, n - block, n_blocks).astype(np.int64)
+    starts[1:-1] = (starts[1:-1] // 2) * 2  # keep the even/odd duplicate pairs together
+    return starts
+
+
+def _full_size_checkpoints(init, hulls, substeps, checkpoints, starts, block, hull_ids=None, joints=None):
+    """Steps the whole batch on the GPU and the sampled worlds on the oracle, comparing at every checkpoint (frames)."""
+    n, B = init.shape
+    sel = np.concatenate([np.arange(s, s + block) for s in starts])
+    cpu = xo.rigid38(init[sel]).astype(np.float32)
+    kw = dict(hull_ids=None if hull_ids is None else hull_ids[sel], joints=None if joints is None else joints[sel])
+    J = 0 if joints is None else joints.shape[1]
+    with cs.Worlds(n, B, joints_per_world=J, body_body_contacts=True) as w:
+        for h in hulls:
+            w.add_hull(h)
+        if hull_ids is not None:
+            w.set_hulls(hull_ids)
+        if joints is not None:
+            w.set_joints(joints)
+        w.upload(init)
+        done = 0
+        for frames in checkpoints:
+            w.integrate(DT, substeps, frames - done)
+            st = w.stats()
+            assert st["overflow_worlds"] == 0 and st["nan_worlds"] == 0, (frames, st)
+            xw.step_worlds(cpu, B, list(hulls), DT, substeps, frames - done, threads=xo.hardware_threads(), **kw)
+            done = frames
+            got = np.concatenate([xo.rigid38(w.download(int(s), block)) for s in starts])
+            pos, rot, exact = parity.compare_arrays(got, cpu)
+            assert pos <= parity.POS_TOL and rot <= parity.ROT_TOL, (frames, pos, rot)
+            assert exact, f"frame {frames}: sampled worlds not bit-identical (max pos err {pos}, rot err {rot})"
+        return xo.rigid38(w.download()).reshape(n, B, 38)
+
+
+def test_c3_full_size_properties_and_sampled_parity(world_path):
+    """C3 at BASELINE size (100k worlds x 10 cubes, default schedule): 1 024 sampled worlds (8 blocks of 128) compared
+    with the oracle after 1, 10, 60 and 600 frames; duplicated worlds give identical results,
+    no NaN, no overflow, stacks stay stacks.  Oracle time: 1 024 worlds x 600 frames = 1.2e8 body-substeps, ~2 min."""
+    if world_path == "fused":
+        pytest.skip("full-size C3 is the staged pipeline's case; the fused kernel is covered at reduced size")
     n = 100_000
     init = scenes.c3_stack(n)
     init[1::2] = init[0::2]
-    frames = 20
-    gpu, _ = _run_gpu(init, [CUBE], frames, 20)
-    g = xo.rigid38(gpu).reshape(n, 10, 38)
+    g = _full_size_checkpoints(init, [CUBE], 20, (1, 10, 60, 600), _sample_blocks(n, 8, 128), 128)
     assert np.isfinite(g).all()
     assert np.array_equal(g[0::2], g[1::2])
     assert np.abs(g[:, :, 33] - np.arange(10)[None, :]).max() < 0.02
-    idx = np.arange(0, n, 1563)
-    cpu, _ = _run_cpu(init[idx], [CUBE], frames, 20)
-    assert np.array_equal(g[idx].reshape(-1, 38), cpu.astype(np.float64))
 
 
 def test_c4_pile_mixed_quickhull_hulls_with_joints():
@@ -333,19 +398,15 @@ def test_large_world_without_pair_table(world_path):
 
 
 def test_c4_full_size_properties_and_sampled_parity(world_path):
-    """C4 at BASELINE size (16 384 worlds x 64 bodies, 32 joints): duplicated worlds give identical results, no NaN,
-    no capacity overflow, nothing tunnels through the ground; a sample of worlds is compared with the oracle."""
+    """C4 at BASELINE size (16 384 worlds x 64 bodies, 32 joints): 256 sampled worlds (8 blocks of 32) compared with the
+    oracle after 1, 10, 60 and 200 frames; duplicated worlds give identical results, no NaN, no capacity overflow,
+    nothing tunnels through the ground.  Oracle time: 256 worlds x 200 frames = 6.6e7 body-substeps, ~10 s."""
     if world_path == "fused":
         pytest.skip("full-size C4 is the staged pipeline's case; the fused kernel is covered at reduced size")
     n = 16_384
     init, hulls, ids, joints = scenes.c4_pile(n)
     init[1::2], ids[1::2], joints[1::2] = init[0::2], ids[0::2], joints[0::2]
-    frames = 12
-    gpu, _ = _run_gpu(init, hulls, frames, 20, hull_ids=ids, joints=joints)
-    g = xo.rigid38(gpu).reshape(n, 64, 38)
+    g = _full_size_checkpoints(init, hulls, 20, (1, 10, 60, 200), _sample_blocks(n, 8, 32), 32, hull_ids=ids, joints=joints)
     assert np.isfinite(g).all()
     assert np.array_equal(g[0::2], g[1::2])
     assert g[:, :, 33].min() > -0.5
-    idx = np.arange(0, n, 2731)
-    cpu, _ = _run_cpu(init[idx], hulls, frames, 20, hull_ids=ids[idx], joints=joints[idx])
-    assert np.array_equal(g[idx].reshape(-1, 38), cpu.astype(np.float64))
