@@ -510,6 +510,7 @@ struct ClipLocal {
     XD float depth(int k) const { return dep[k]; }
     XD void set_depth(int k, float d) { dep[k] = d; }
     XD bool overflowed() const { return false; }
+    XD void reset() {}
 };
 // ClipShared: the same arrays in shared memory, word-interleaved across the block's threads (bank-conflict free),
 // with room for CAP <= kMaxClip entries.  A convex polygon gains at most one vertex per clip plane, so
@@ -534,6 +535,7 @@ struct ClipShared {
     XD float depth(int k) const { return base[(6 * CAP + (k < CAP ? k : CAP - 1)) * STRIDE]; }
     XD void set_depth(int k, float d) { if (k < CAP) base[(6 * CAP + k) * STRIDE] = d; }
     XD bool overflowed() const { return over; }
+    XD void reset() { over = false; }
 };
 
 // Clip polygon `src` (n points) against the half-space dot(s, p - o) <= 0 into polygon `dst`.

@@ -13,8 +13,11 @@
 //                   constants after unrolling), B's 12 edge vectors during the cull;
 //   shared memory : a per-thread copy of the 16 vertices as float4 [vertex][thread] (LDS.128, conflict-free for any
 //                   vertex index) for the accesses whose vertex index is hull data (edge end points, witnesses), and
-//                   the per-thread survivor masks of the cull, 12 bits per edge of A, [edge][thread].
+//                   the per-thread survivor masks of the cull, 12 bits per edge of A.
 // No two threads share scratch, so the kernel has no barrier after the hull table is staged.
+// kFuse: the manifold stage (Sutherland-Hodgman clipping -> the pair's <= 4 contacts) runs as the epilogue of the same
+// thread, reusing the scratch column, instead of as a kernel of its own (one launch, one work-list pass and the
+// latency-bound tail of stage_manifold_kernel less per substep).
 #pragma once
 
 namespace xpbd {
@@ -23,8 +26,9 @@ constexpr int kSatThreadBlock = 128;
 #ifndef XPBD_SAT_THREAD_MIN_BLOCKS
 #define XPBD_SAT_THREAD_MIN_BLOCKS 4
 #endif
+constexpr int kSatThreadSlots = 19;  // float4 slots per thread: 0..15 the vertices, 16..18 the survivor masks (12 words)
 __host__ __device__ inline size_t sat_thread_smem_bytes(uint32_t hull_blob_bytes) {
-    return (size_t)hull_blob_bytes + (size_t)kSatThreadBlock * (16 * sizeof(float4) + 12 * sizeof(uint32_t));
+    return (size_t)hull_blob_bytes + (size_t)kSatThreadBlock * kSatThreadSlots * sizeof(float4);
 }
 
 // sqrt for the witness heuristic only (never feeds a result): one MUFU instead of the correctly rounded sequence
@@ -34,10 +38,29 @@ XD float sqrt_approx(float x) {
     return r;
 }
 
+// The thread's scratch: one COLUMN of float4 slots, [slot][thread] (a thread only ever touches its own column, so
+// different phases may reuse the slots without any synchronisation).
 struct SatThreadScratch {
-    float4* W;      // [16][kSatThreadBlock], already offset by the thread index: A's vertices 0..7, B's 8..15
-    uint32_t* M;    // [12][kSatThreadBlock], offset by the thread index
-    XD V3 vert(int v) const { const float4 x = W[v * kSatThreadBlock]; return v3(x.x, x.y, x.z); }
+    float4* col;  // already offset by the thread index: slots 0..7 A's vertices, 8..15 B's, 16..18 survivor masks
+    XD V3 vert(int v) const { const float4 x = col[v * kSatThreadBlock]; return v3(x.x, x.y, x.z); }
+    XD void set_vert(int v, float4 x) const { col[v * kSatThreadBlock] = x; }
+    XD uint32_t* mask(int ia) const { return reinterpret_cast<uint32_t*>(col + (16 + (ia >> 2)) * kSatThreadBlock) + (ia & 3); }
+};
+// Clip scratch of the manifold epilogue (interface of ClipShared, 8 entries per buffer — cube-shaped hulls with quad faces),
+// in the same column: the two polygon buffers take slots 0..15 (one LDS.128 / STS.128 per point), the depths slots 16..17.
+// The vertices and masks that lived there are dead by then; face_manifold reads the hull vertices from global memory.
+struct ClipColumns {
+    float4* col;
+    bool over = false;
+    XD V3 get(int w, int k) const { k = k < 8 ? k : 7; const float4 x = col[(w * 8 + k) * kSatThreadBlock]; return v3(x.x, x.y, x.z); }
+    XD void set(int w, int k, V3 v) {
+        if (k >= 8) { over = true; return; }
+        col[(w * 8 + k) * kSatThreadBlock] = make_float4(v.x, v.y, v.z, 0.0f);
+    }
+    XD float depth(int k) const { k = k < 8 ? k : 7; return reinterpret_cast<const float*>(col + (16 + (k >> 2)) * kSatThreadBlock)[k & 3]; }
+    XD void set_depth(int k, float d) { if (k < 8) reinterpret_cast<float*>(col + (16 + (k >> 2)) * kSatThreadBlock)[k & 3] = d; }
+    XD bool overflowed() const { return over; }
+    XD void reset() { over = false; }
 };
 
 // face_axes_separation (src/collision.rs:123-149) of a 6-face hull against 8 vertices `WO` of the other hull; L = those
@@ -86,7 +109,7 @@ XD int2 witness_vertices_thread(float4 plane, const V3 (&L)[8]) {
     return make_int2(v1, v2);
 }
 
-template <bool kCull>
+template <bool kCull, bool kFuse>
 XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, const SatThreadScratch& S) {
     const int B = P.B, maxV = P.S.maxV;
     const int64_t world = d.w;
@@ -105,7 +128,7 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
         for (int v = 0; v < 8; ++v) {
             const float4 x = P.S.verts[gi * maxV + v], y = P.S.verts[gj * maxV + v];
             WA[v] = v3(x.x, x.y, x.z); WB[v] = v3(y.x, y.y, y.z);
-            S.W[v * kSatThreadBlock] = x; S.W[(8 + v) * kSatThreadBlock] = y;
+            S.set_vert(v, x); S.set_vert(8 + v, y);
             if (kCull) rkey = max(rkey, max(abs_coord_key(x), abs_coord_key(y)));
         }
         const float4 ra = P.bodies.dynC[gi], rb = P.bodies.dynC[gj];
@@ -138,20 +161,22 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
                 const int2 ea = EA[ia];
                 const V3 foot = S.vert(ea.x);
                 const V3 edge_a = S.vert(ea.y) - foot;
+                // per edge of A: the three vectors every pair of this edge is tested against (the estimate c . (w - foot) is
+                // taken as one dot product with the difference: fewer operations and less cancellation than c.w - c.foot)
+                const V3 d1 = cull.w1 - foot, d2 = cull.w2 - foot, dC = foot - CA;
                 uint32_t bits = 0;
 #pragma unroll
                 for (int jb = 0; jb < 12; ++jb) {
                     const V3 c = cross(edge_a, eb[jb]);
                     const float c2 = dot(c, c);
-                    const float df = dot(c, foot);
-                    const float f = df - dot(c, CA);
-                    const float u1 = dot(c, cull.w1) - df, u2 = dot(c, cull.w2) - df;
+                    const float f = dot(c, dC);
+                    const float u1 = dot(c, d1), u2 = dot(c, d2);
                     const float us = f < 0.0f ? -fmaxf(u1, u2) : fminf(u1, u2);  // the smaller of the two bounds, flipped like the axis
                     const bool below = us < 0.0f && fmul(us, us) > fmul(K, c2) && fmul(f, f) > fmul(Kf, c2) && c2 > 1e-24f;
                     const bool keep = !below && c2 > 0.0f;
                     bits |= (keep ? 1u : 0u) << jb;
                 }
-                S.M[ia * kSatThreadBlock] = bits;
+                *S.mask(ia) = bits;
             }
         }
         // ---- stage 2: the reference's arithmetic (src/collision.rs:166-193) for the surviving pairs, in scan order
@@ -160,33 +185,41 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
         for (int v = 0; v < 8; ++v) { XA[v] = S.vert(v); XB[v] = S.vert(8 + v); }
         float best = -FLT_MAX;
         int bi = -1;
-#pragma unroll 1
-        for (int ia = 0; ia < 12; ++ia) {
-            uint32_t bits = kCull ? S.M[ia * kSatThreadBlock] : 0xfffu;
-            if (!bits) continue;
-            const int2 ea = EA[ia];
-            const V3 foot = S.vert(ea.x);
-            const V3 edge_a = S.vert(ea.y) - foot;
-            const V3 fc = foot - CA;
-            while (bits) {
-                const int jb = __ffs((int)bits) - 1;
-                bits &= bits - 1;
-                const int2 e = EB[jb];
-                const V3 edge_b = S.vert(8 + e.y) - S.vert(8 + e.x);
-                V3 axis = normalize(cross(edge_a, edge_b));  // parallel edges -> NaN axis, no guard (as the reference)
-                if (dot(axis, fc) < 0.0f) axis = -axis;
-                // Ignore if another point on `a` is further in the direction to `b`.
-                float sa = dot(axis, XA[0]);
-#pragma unroll
-                for (int v = 1; v < 8; ++v) sa = fmaxf(sa, dot(axis, XA[v]));
-                if (sa > dot(foot, axis)) continue;
-                const float disp = plane_displacement(foot, axis);
-                float sb = dot(axis, XB[0]);
-#pragma unroll
-                for (int v = 1; v < 8; ++v) sb = fminf(sb, dot(axis, XB[v]));
-                const float distance = fsub(sb, disp);
-                if (distance > best) { best = distance; bi = ia * 12 + jb; }  // serial scan: strict > keeps the first maximum
+        // Every lane walks ITS OWN survivors (edge of A by edge of A, set bit by set bit), so a warp iterates
+        // max-over-lanes(survivor count) times; a loop over the edges of A with an inner loop over the bits would iterate
+        // sum-over-edges(max-over-lanes(bits of that edge)) times (measured: 32.7 instead of ~24 per warp on C3).
+        int ia = -1;
+        uint32_t bits = 0;
+        V3 foot = v3(0.f, 0.f, 0.f), edge_a = foot, fc = foot;
+        for (;;) {
+            if (bits == 0) {
+                do {
+                    if (++ia >= 12) break;
+                    bits = kCull ? *S.mask(ia) : 0xfffu;
+                } while (bits == 0);
+                if (ia >= 12) break;
+                const int2 ea = EA[ia];
+                foot = S.vert(ea.x);
+                edge_a = S.vert(ea.y) - foot;
+                fc = foot - CA;
             }
+            const int jb = __ffs((int)bits) - 1;
+            bits &= bits - 1;
+            const int2 e = EB[jb];
+            const V3 edge_b = S.vert(8 + e.y) - S.vert(8 + e.x);
+            V3 axis = normalize(cross(edge_a, edge_b));  // parallel edges -> NaN axis, no guard (as the reference)
+            if (dot(axis, fc) < 0.0f) axis = -axis;
+            // Ignore if another point on `a` is further in the direction to `b`.
+            float sa = dot(axis, XA[0]);
+#pragma unroll
+            for (int v = 1; v < 8; ++v) sa = fmaxf(sa, dot(axis, XA[v]));
+            if (sa > dot(foot, axis)) continue;
+            const float disp = plane_displacement(foot, axis);
+            float sb = dot(axis, XB[0]);
+#pragma unroll
+            for (int v = 1; v < 8; ++v) sb = fminf(sb, dot(axis, XB[v]));
+            const float distance = fsub(sb, disp);
+            if (distance > best) { best = distance; bi = ia * 12 + jb; }  // serial scan: strict > keeps the first maximum
         }
         de = best; ep = bi;
         if (!(de >= 0.0f)) pf = choose_feature(da, fa, db, fb, de, ep);
@@ -194,20 +227,23 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
 done:
     P.S.pairs[d.x].y = pf.feature;
     P.S.pairs[d.x].z = pf.index;
+    if (kFuse) {  // stage 3 as the epilogue: clipping -> the pair's contacts (see manifold_candidate)
+        ClipColumns clip{S.col};
+        manifold_candidate(P, T, (uint32_t)d.x, make_int4(d.y, pf.feature, pf.index, 0), clip);
+    }
 }
 
-template <bool kCull>
+template <bool kCull, bool kFuse>
 __global__ void __launch_bounds__(kSatThreadBlock, XPBD_SAT_THREAD_MIN_BLOCKS) stage_sat_thread_kernel(StagedParams P) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ __align__(8) uint64_t bar;
     stage_bulk(smem, P.hull_blob, P.hull_blob_bytes, &bar, reinterpret_cast<unsigned int*>(P.counters + 2));
     const HullTable T{smem};
     SatThreadScratch S;
-    S.W = reinterpret_cast<float4*>(smem + P.hull_blob_bytes / 4) + threadIdx.x;
-    S.M = reinterpret_cast<uint32_t*>(reinterpret_cast<float4*>(smem + P.hull_blob_bytes / 4) + 16 * kSatThreadBlock) + threadIdx.x;
+    S.col = reinterpret_cast<float4*>(smem + P.hull_blob_bytes / 4) + threadIdx.x;
     const unsigned count = *P.S.work_count;
     for (unsigned it = blockIdx.x * blockDim.x + threadIdx.x; it < count; it += gridDim.x * blockDim.x)
-        sat_thread_candidate<kCull>(P, T, P.S.worklist[it], S);
+        sat_thread_candidate<kCull, kFuse>(P, T, P.S.worklist[it], S);
 }
 
 }  // namespace xpbd

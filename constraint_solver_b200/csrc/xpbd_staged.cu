@@ -457,6 +457,57 @@ __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_cubes_kern
     }
 }
 
+// Manifold of one candidate whose SAT result is in pr (.x = i | j << 16, .y = feature, .z = index): clipping -> <= 4 fresh
+// contacts in the pair's slot, count in pairs[slot].w.  Shared by stage_manifold_kernel (thread per candidate) and by the
+// thread-per-candidate SAT kernel, which runs it as its epilogue.
+template <class Clip>
+XD void manifold_candidate(const StagedParams& P, const HullTable& T, uint32_t slot, int4 pr, Clip& clip) {
+    const int B = P.B, maxV = P.S.maxV;
+    int n_out = 0;
+    if (pr.y != kNone) {
+        const int64_t world = slot / (uint32_t)P.S.capP;
+        const int i = pr.x & 0xffff, j = pr.x >> 16;
+        const int64_t gi = world * B + i, gj = world * B + j;
+        PairFeature pf; pf.feature = pr.y; pf.index = pr.z;
+        const float4 ra = P.bodies.dynC[gi], rb = P.bodies.dynC[gj];
+        const float4 pa = P.S.fpos[gi], pb = P.S.fpos[gj];
+        Fr FA, FB;
+        FA.p = v3(pa.x, pa.y, pa.z); FA.q = q4(ra.w, ra.x, ra.y, ra.z);
+        FB.p = v3(pb.x, pb.y, pb.z); FB.q = q4(rb.w, rb.x, rb.y, rb.z);
+        Manifold m;
+        int incident;
+        const HullDesc& hA = T.desc(P.hull_ids ? P.hull_ids[gi] : 0);
+        const HullDesc& hB = T.desc(P.hull_ids ? P.hull_ids[gj] : 0);
+        const float* WA = reinterpret_cast<const float*>(P.S.verts + gi * maxV);
+        const float* WB = reinterpret_cast<const float*>(P.S.verts + gj * maxV);
+        clip.reset();
+        pair_manifold(T, hA, hB, FA, FB, WA, WB, pf, clip, m, incident);
+        if (clip.overflowed()) pair_manifold(T, hA, hB, FA, FB, WA, WB, pf, m, incident);  // never seen; exact by construction
+        const int inc = incident == 0 ? i : j, oth = incident == 0 ? j : i;
+        const int64_t ginc = world * B + inc, goth = world * B + oth;
+        const float4 qi = P.bodies.dynC[ginc], qo = P.bodies.dynC[goth];
+        const float4 fi = P.S.finvp[ginc], fo = P.S.finvp[goth];
+        Fr finvI, finvO;
+        finvI.q = conjugate(q4(qi.w, qi.x, qi.y, qi.z)); finvI.p = v3(fi.x, fi.y, fi.z);
+        finvO.q = conjugate(q4(qo.w, qo.x, qo.y, qo.z)); finvO.p = v3(fo.x, fo.y, fo.z);
+        float4* out = P.S.pcons + (size_t)slot * kMaxManifold * 3;
+#pragma unroll
+        for (int k = 0; k < kMaxManifold; ++k) {
+            if (k >= m.count) continue;
+            const V3 correction = m.target[k] - m.point[k];
+            if (magnitude2(correction) == 0.0f) continue;  // no direction: dropped
+            const V3 a = finvI * m.point[k];
+            const V3 b = finvO * m.target[k];
+            const V3 n = normalize(correction);
+            out[3 * n_out + 0] = make_float4(__int_as_float(cons_head(kContact, inc, oth)), a.x, a.y, a.z);
+            out[3 * n_out + 1] = make_float4(b.x, b.y, b.z, 0.f);
+            out[3 * n_out + 2] = make_float4(n.x, n.y, n.z, 0.f);
+            ++n_out;
+        }
+    }
+    P.S.pairs[slot].w = n_out;
+}
+
 }  // namespace xpbd
 #include "xpbd_sat_thread.cuh"  // stage_sat_thread_kernel: thread per candidate (cube-shaped hulls)
 namespace xpbd {
@@ -475,57 +526,13 @@ __global__ void __launch_bounds__(kManifoldThreads, XPBD_MANIFOLD_MIN_BLOCKS) st
     __shared__ __align__(8) uint64_t bar;
     stage_bulk(smem, P.hull_blob, P.hull_blob_bytes, &bar, reinterpret_cast<unsigned int*>(P.counters + 2));
     const HullTable T{smem};
-    const int B = P.B, maxV = P.S.maxV;
     const unsigned count = *P.S.work_count;
     // clip polygons live in shared memory (thread-private arrays would be local memory: ~0.5 KB per candidate of
     // L2/HBM round trips, measured as 3x the stage's algorithmic traffic)
     ClipShared<CAP, kManifoldThreads> clip{reinterpret_cast<float*>(smem) + P.hull_blob_bytes / 4 + threadIdx.x};
     for (unsigned it = blockIdx.x * blockDim.x + threadIdx.x; it < count; it += gridDim.x * blockDim.x) {
         const uint32_t slot = (uint32_t)P.S.worklist[it].x;
-        const int4 pr = P.S.pairs[slot];
-        int n_out = 0;
-        if (pr.y != kNone) {
-            const int64_t world = slot / (uint32_t)P.S.capP;
-            const int i = pr.x & 0xffff, j = pr.x >> 16;
-            const int64_t gi = world * B + i, gj = world * B + j;
-            PairFeature pf; pf.feature = pr.y; pf.index = pr.z;
-            const float4 ra = P.bodies.dynC[gi], rb = P.bodies.dynC[gj];
-            const float4 pa = P.S.fpos[gi], pb = P.S.fpos[gj];
-            Fr FA, FB;
-            FA.p = v3(pa.x, pa.y, pa.z); FA.q = q4(ra.w, ra.x, ra.y, ra.z);
-            FB.p = v3(pb.x, pb.y, pb.z); FB.q = q4(rb.w, rb.x, rb.y, rb.z);
-            Manifold m;
-            int incident;
-            const HullDesc& hA = T.desc(P.hull_ids ? P.hull_ids[gi] : 0);
-            const HullDesc& hB = T.desc(P.hull_ids ? P.hull_ids[gj] : 0);
-            const float* WA = reinterpret_cast<const float*>(P.S.verts + gi * maxV);
-            const float* WB = reinterpret_cast<const float*>(P.S.verts + gj * maxV);
-            clip.over = false;
-            pair_manifold(T, hA, hB, FA, FB, WA, WB, pf, clip, m, incident);
-            if (clip.over) pair_manifold(T, hA, hB, FA, FB, WA, WB, pf, m, incident);  // never seen; exact by construction
-            const int inc = incident == 0 ? i : j, oth = incident == 0 ? j : i;
-            const int64_t ginc = world * B + inc, goth = world * B + oth;
-            const float4 qi = P.bodies.dynC[ginc], qo = P.bodies.dynC[goth];
-            const float4 fi = P.S.finvp[ginc], fo = P.S.finvp[goth];
-            Fr finvI, finvO;
-            finvI.q = conjugate(q4(qi.w, qi.x, qi.y, qi.z)); finvI.p = v3(fi.x, fi.y, fi.z);
-            finvO.q = conjugate(q4(qo.w, qo.x, qo.y, qo.z)); finvO.p = v3(fo.x, fo.y, fo.z);
-            float4* out = P.S.pcons + (size_t)slot * kMaxManifold * 3;
-#pragma unroll
-            for (int k = 0; k < kMaxManifold; ++k) {
-                if (k >= m.count) continue;
-                const V3 correction = m.target[k] - m.point[k];
-                if (magnitude2(correction) == 0.0f) continue;  // no direction: dropped
-                const V3 a = finvI * m.point[k];
-                const V3 b = finvO * m.target[k];
-                const V3 n = normalize(correction);
-                out[3 * n_out + 0] = make_float4(__int_as_float(cons_head(kContact, inc, oth)), a.x, a.y, a.z);
-                out[3 * n_out + 1] = make_float4(b.x, b.y, b.z, 0.f);
-                out[3 * n_out + 2] = make_float4(n.x, n.y, n.z, 0.f);
-                ++n_out;
-            }
-        }
-        P.S.pairs[slot].w = n_out;
+        manifold_candidate(P, T, slot, P.S.pairs[slot], clip);
     }
 }
 
@@ -733,6 +740,7 @@ struct StagedState {
     int B = 0;
     int grid_prepare = 0, grid_sat = 0, grid_manifold = 0;
     size_t smem_prepare = 0, smem_sat = 0, smem_manifold = 0;
+    bool fuse_manifold = false;   // sat_fn also writes the manifolds (thread-per-candidate kernel): no stage_manifold launch
     int sat_threads = 256;        // block size of sat_fn
     int sat_cands_per_block = 8;  // candidates one block of sat_fn takes per grid-stride round
     int warps_prepare = 8;
@@ -875,7 +883,10 @@ static int build_staged(xpbd_batch* b, StagedState* st) {
                 st->sat_fn = cull ? stage_sat_cubes_kernel<true> : stage_sat_cubes_kernel<false>;
                 st->sat_cands_per_block = 16;
             } else {
-                st->sat_fn = cull ? stage_sat_thread_kernel<true> : stage_sat_thread_kernel<false>;
+                const char* fz = std::getenv("XPBD_SAT_FUSE");  // "0": keep stage_manifold as a kernel of its own (A/B runs)
+                st->fuse_manifold = !(fz && fz[0] == '0') && H.max_face_verts <= 4;
+                st->sat_fn = st->fuse_manifold ? (cull ? stage_sat_thread_kernel<true, true> : stage_sat_thread_kernel<false, true>)
+                                               : (cull ? stage_sat_thread_kernel<true, false> : stage_sat_thread_kernel<false, false>);
                 st->sat_threads = kSatThreadBlock;
                 st->sat_cands_per_block = kSatThreadBlock;
                 st->smem_sat = sat_thread_smem_bytes(H.bytes);
@@ -1035,7 +1046,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
             if (timed) cudaEventRecord(b->ev_stage[1], stream);
             if (P.body_body) st->sat_fn<<<grid_sat, st->sat_threads, st->smem_sat, stream>>>(Q);
             if (timed) cudaEventRecord(b->ev_stage[2], stream);
-            if (P.body_body) st->manifold_fn<<<grid_manifold, kManifoldThreads, st->smem_manifold, stream>>>(Q);
+            if (P.body_body && !st->fuse_manifold) st->manifold_fn<<<grid_manifold, kManifoldThreads, st->smem_manifold, stream>>>(Q);
             if (timed) cudaEventRecord(b->ev_stage[3], stream);
             stage_solve_kernel<<<grid_solve, 128, 0, stream>>>(Q);
             if (timed) cudaEventRecord(b->ev_stage[4], stream);
@@ -1055,7 +1066,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
     b->last.sub_batches = n_sub;
     b->stage_timed = true;
     XPBD_CUDA_TRY(cudaGetLastError());
-    b->last.kernel_launches = n_sub * total * (P.body_body ? 4 : 2);
+    b->last.kernel_launches = n_sub * total * (P.body_body ? (st->fuse_manifold ? 3 : 4) : 2);
     return XPBD_OK;
 }
 
@@ -1148,7 +1159,7 @@ extern "C" int xpbd_sat_feature_batch(const xpbd_frame* fa, const xpbd_frame* fb
     size_t smem = dev.bytes + 8 * (size_t)sat_words_per_warp(maxV) * 4;
     if (schedule == 0) fn = cull ? stage_sat_kernel<true> : stage_sat_kernel<false>;
     else if (schedule == 1) fn = cull ? stage_sat_cubes_kernel<true> : stage_sat_cubes_kernel<false>;
-    else { fn = cull ? stage_sat_thread_kernel<true> : stage_sat_thread_kernel<false>; threads = kSatThreadBlock; smem = sat_thread_smem_bytes(dev.bytes); }
+    else { fn = cull ? stage_sat_thread_kernel<true, false> : stage_sat_thread_kernel<false, false>; threads = kSatThreadBlock; smem = sat_thread_smem_bytes(dev.bytes); }
     XPBD_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 1, n_sm = 148, devid = 0;
     XPBD_CUDA_TRY(cudaGetDevice(&devid));

@@ -280,7 +280,8 @@ def test_sub_batches_stats_sum_over_ranges(world_path):
             w.integrate(DT, 20, 15)
             st = w.stats()
             res.append((st["constraints"], st["candidate_pairs"], st["overflow_worlds"]))
-            assert st["sub_batches"] == k and st["kernel_launches"] == k * 4 * 20 * 15 + 1  # + the NaN-world count
+            # prepare, SAT (+ manifold as its epilogue for all-cube batches), [manifold,] solve per substep and range; + the NaN-world count
+            assert st["sub_batches"] == k and st["kernel_launches"] in (k * 3 * 20 * 15 + 1, k * 4 * 20 * 15 + 1)
     assert res[0] == res[1] and res[0][1] > 0
 
 
