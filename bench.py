@@ -132,7 +132,7 @@ def cpu_baseline(workload: str, cfg: dict, seconds_target: float = 12.0, dtype=n
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as xo
     import bench_oracle
-    return bench_oracle.time_oracle(workload, cfg, seconds_target, dtype, make_scene)
+    return bench_oracle.time_oracle(workload, cfg, seconds_target, dtype)
 
 
 def run_reference(args, cfg, rank):
@@ -142,7 +142,7 @@ def run_reference(args, cfg, rank):
         return
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import bench_oracle
-    res = bench_oracle.run_reference_arm(args.workload, cfg, args.steps, args.warmup, make_scene)
+    res = bench_oracle.run_reference_arm(args.workload, cfg, args.steps, args.warmup)
     line = {
         "impl": "reference", "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True,

@@ -564,10 +564,11 @@ XD int clip_polygon(Clip& C, int src, int n, V3 o, V3 s, int dst) {
 }
 
 // Face contact: reference body R (face r, frame FR, world verts WR), incident body I.  One lane.
-template <class Clip>
+// emit(point, target) is called once per kept contact, in polygon order: point on the incident body, target = its
+// projection on the reference plane.
+template <class Clip, class Emit>
 XD void face_manifold(const HullTable& T, const HullDesc& hR, const HullDesc& hI, const Fr& FR, const Fr& FI,
-                      const float* WR, const float* WI, int r, Clip& C, Manifold& out) {
-    out.count = 0;
+                      const float* WR, const float* WI, int r, Clip& C, Emit& emit) {
     // ref_plane = frames.0 * polytopes.0.plane(face)  (src/collision.rs:66, src/frame.rs:55-64)
     const float4 pl = T.plane(hR, r);
     const V3 nl = v3(pl.x, pl.y, pl.z);
@@ -639,22 +640,19 @@ XD void face_manifold(const HullTable& T, const HullDesc& hR, const HullDesc& hI
         XPBD_CSWAP(k0, k1) XPBD_CSWAP(k2, k3) XPBD_CSWAP(k0, k2) XPBD_CSWAP(k1, k3) XPBD_CSWAP(k1, k2)
 #undef XPBD_CSWAP
     }
-    const int kept[kMaxManifold] = {k0, k1, k2, k3};
-#pragma unroll
-    for (int k = 0; k < kMaxManifold; ++k) {
-        if (k < nk) {
-            const V3 p = C.get(dst, kept[k]);
-            out.point[k] = p;
-            out.target[k] = p - C.depth(kept[k]) * n;  // Plane::project
-        }
+#pragma unroll 1
+    for (int k = 0; k < nk; ++k) {  // rolled: one copy of the caller's contact code
+        const int kk = k == 0 ? k0 : (k == 1 ? k1 : (k == 2 ? k2 : k3));
+        const V3 p = C.get(dst, kk);
+        emit(p, p - C.depth(kk) * n);  // Plane::project
     }
-    out.count = nk;
 }
 
 XD float clamp01(float x) { return x < 0.0f ? 0.0f : (x > 1.0f ? 1.0f : x); }
 
 // Closest points of the two edges (Ericson 5.1.9).  One lane.
-XD void edge_manifold(V3 p1, V3 q1, V3 p2, V3 q2, Manifold& out) {
+template <class Emit>
+XD void edge_manifold(V3 p1, V3 q1, V3 p2, V3 q2, Emit& emit) {
     const V3 d1 = q1 - p1, d2 = q2 - p2, r = p1 - p2;
     const float a = dot(d1, d1), e = dot(d2, d2), f = dot(d2, r);
     const float c = dot(d1, r), b = dot(d1, d2);
@@ -663,34 +661,56 @@ XD void edge_manifold(V3 p1, V3 q1, V3 p2, V3 q2, Manifold& out) {
     float t = fdiv(fadd(fmul(b, s), f), e);
     if (t < 0.0f) { t = 0.0f; s = clamp01(fdiv(-c, a)); }
     else if (t > 1.0f) { t = 1.0f; s = clamp01(fdiv(fsub(b, c), a)); }
-    out.point[0] = p1 + d1 * s;
-    out.target[0] = p2 + d2 * t;
-    out.count = 1;
+    emit(p1 + d1 * s, p2 + d2 * t);
 }
 
-// Manifold of one pair from its chosen feature. `incident` = 0: contact points ride on A, 1: on B.
-template <class Clip>
-XD void pair_manifold(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const Fr& FA, const Fr& FB,
-                      const float* WA, const float* WB, PairFeature pf, Clip& C, Manifold& m, int& incident) {
-    m.count = 0;
-    incident = 0;
+// Which body carries the contact points of a feature: 0 = A, 1 = B (kFaceA: A is the reference, B's face is clipped).
+XD int feature_incident(int feature) { return feature == kFaceA ? 1 : 0; }
+
+// Manifold of one pair from its chosen feature: emit(point, target) per contact, point on body feature_incident(feature).
+// The two face cases share ONE inlined copy of face_manifold (operands selected, not two call sites): the clipping code
+// is the bulk of the manifold stage's instruction footprint.
+template <class Clip, class Emit>
+XD void pair_manifold_emit(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const Fr& FA, const Fr& FB,
+                           const float* WA, const float* WB, PairFeature pf, Clip& C, Emit& emit) {
     if (pf.feature == kEdgeEdge) {
         const int ia = pf.index / hB.n_edges, jb = pf.index - ia * hB.n_edges;
         const int2 ea = T.edge(hA, ia), eb = T.edge(hB, jb);
-        edge_manifold(ld3(WA, ea.x), ld3(WA, ea.y), ld3(WB, eb.x), ld3(WB, eb.y), m);
-        incident = 0;
-    } else if (pf.feature == kFaceB) {
-        face_manifold(T, hB, hA, FB, FA, WB, WA, pf.index, C, m);  // B is the reference, A's face is clipped
-        incident = 0;
-    } else if (pf.feature == kFaceA) {
-        face_manifold(T, hA, hB, FA, FB, WA, WB, pf.index, C, m);
-        incident = 1;
+        edge_manifold(ld3(WA, ea.x), ld3(WA, ea.y), ld3(WB, eb.x), ld3(WB, eb.y), emit);
+    } else if (pf.feature == kFaceA || pf.feature == kFaceB) {
+        const bool refB = pf.feature == kFaceB;  // B is the reference, A's face is clipped: the points ride on A
+        const HullDesc& hR = refB ? hB : hA;
+        const HullDesc& hI = refB ? hA : hB;
+        Fr FR, FI;
+        FR.p = refB ? FB.p : FA.p; FR.q = refB ? FB.q : FA.q;
+        FI.p = refB ? FA.p : FB.p; FI.q = refB ? FA.q : FB.q;
+        face_manifold(T, hR, hI, FR, FI, refB ? WB : WA, refB ? WA : WB, pf.index, C, emit);
     }
 }
+// The specification's own scratch (thread-private arrays of kMaxClip entries): the fallback for a polygon that outgrew a
+// smaller shared-memory scratch (face_manifold returns before its first emit then).  Never seen in practice and kept out
+// of line, so that it costs no instruction-cache footprint on the paths that run.
+template <class Emit>
+__device__ __noinline__ void pair_manifold_local_emit(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const Fr& FA,
+                                                      const Fr& FB, const float* WA, const float* WB, PairFeature pf, Emit& emit) {
+    ClipLocal C;
+    pair_manifold_emit(T, hA, hB, FA, FB, WA, WB, pf, C, emit);
+}
+
+// The same into a Manifold record (the fused world kernel and the per-function query kernels).
+struct ManifoldFill {
+    Manifold& m;
+    XD void operator()(V3 point, V3 target) {
+        if (m.count < kMaxManifold) { m.point[m.count] = point; m.target[m.count] = target; ++m.count; }
+    }
+};
 XD void pair_manifold(const HullTable& T, const HullDesc& hA, const HullDesc& hB, const Fr& FA, const Fr& FB,
                       const float* WA, const float* WB, PairFeature pf, Manifold& m, int& incident) {
+    m.count = 0;
+    incident = feature_incident(pf.feature);
     ClipLocal C;
-    pair_manifold(T, hA, hB, FA, FB, WA, WB, pf, C, m, incident);
+    ManifoldFill fill{m};
+    pair_manifold_emit(T, hA, hB, FA, FB, WA, WB, pf, C, fill);
 }
 
 }  // namespace xpbd

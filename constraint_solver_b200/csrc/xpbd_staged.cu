@@ -474,36 +474,35 @@ XD void manifold_candidate(const StagedParams& P, const HullTable& T, uint32_t s
         Fr FA, FB;
         FA.p = v3(pa.x, pa.y, pa.z); FA.q = q4(ra.w, ra.x, ra.y, ra.z);
         FB.p = v3(pb.x, pb.y, pb.z); FB.q = q4(rb.w, rb.x, rb.y, rb.z);
-        Manifold m;
-        int incident;
         const HullDesc& hA = T.desc(P.hull_ids ? P.hull_ids[gi] : 0);
         const HullDesc& hB = T.desc(P.hull_ids ? P.hull_ids[gj] : 0);
         const float* WA = reinterpret_cast<const float*>(P.S.verts + gi * maxV);
         const float* WB = reinterpret_cast<const float*>(P.S.verts + gj * maxV);
-        clip.reset();
-        pair_manifold(T, hA, hB, FA, FB, WA, WB, pf, clip, m, incident);
-        if (clip.overflowed()) pair_manifold(T, hA, hB, FA, FB, WA, WB, pf, m, incident);  // never seen; exact by construction
+        const int incident = feature_incident(pf.feature);
         const int inc = incident == 0 ? i : j, oth = incident == 0 ? j : i;
-        const int64_t ginc = world * B + inc, goth = world * B + oth;
-        const float4 qi = P.bodies.dynC[ginc], qo = P.bodies.dynC[goth];
-        const float4 fi = P.S.finvp[ginc], fo = P.S.finvp[goth];
-        Fr finvI, finvO;
-        finvI.q = conjugate(q4(qi.w, qi.x, qi.y, qi.z)); finvI.p = v3(fi.x, fi.y, fi.z);
-        finvO.q = conjugate(q4(qo.w, qo.x, qo.y, qo.z)); finvO.p = v3(fo.x, fo.y, fo.z);
+        Fr finvI, finvO;  // inverse frames of the incident / the other body (their rotations and frame positions are loaded above)
+        {
+            const float4 fi = P.S.finvp[world * B + inc], fo = P.S.finvp[world * B + oth];
+            finvI.q = conjugate(incident == 0 ? FA.q : FB.q); finvI.p = v3(fi.x, fi.y, fi.z);
+            finvO.q = conjugate(incident == 0 ? FB.q : FA.q); finvO.p = v3(fo.x, fo.y, fo.z);
+        }
         float4* out = P.S.pcons + (size_t)slot * kMaxManifold * 3;
-#pragma unroll
-        for (int k = 0; k < kMaxManifold; ++k) {
-            if (k >= m.count) continue;
-            const V3 correction = m.target[k] - m.point[k];
-            if (magnitude2(correction) == 0.0f) continue;  // no direction: dropped
-            const V3 a = finvI * m.point[k];
-            const V3 b = finvO * m.target[k];
+        const float head = __int_as_float(cons_head(kContact, inc, oth));
+        // one manifold point -> fresh contact constraint in body-local anchors; dropped when point and target coincide
+        auto emit = [&](V3 point, V3 target) {
+            const V3 correction = target - point;
+            if (magnitude2(correction) == 0.0f) return;  // no direction: dropped
+            const V3 a = finvI * point;
+            const V3 b = finvO * target;
             const V3 n = normalize(correction);
-            out[3 * n_out + 0] = make_float4(__int_as_float(cons_head(kContact, inc, oth)), a.x, a.y, a.z);
+            out[3 * n_out + 0] = make_float4(head, a.x, a.y, a.z);
             out[3 * n_out + 1] = make_float4(b.x, b.y, b.z, 0.f);
             out[3 * n_out + 2] = make_float4(n.x, n.y, n.z, 0.f);
             ++n_out;
-        }
+        };
+        clip.reset();
+        pair_manifold_emit(T, hA, hB, FA, FB, WA, WB, pf, clip, emit);
+        if (clip.overflowed()) pair_manifold_local_emit(T, hA, hB, FA, FB, WA, WB, pf, emit);  // never seen; exact by construction
     }
     P.S.pairs[slot].w = n_out;
 }

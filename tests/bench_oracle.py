@@ -5,6 +5,7 @@ import time
 import numpy as np
 
 import oracle_lib as xo
+import oracle_scenes as xs  # scenes built with the oracle only: these legs never import or map the product library
 
 DT = 1.0 / 60.0
 
@@ -12,10 +13,10 @@ DT = 1.0 / 60.0
 class _Sample:
     """A bounded sample of a workload, prepared like the GPU arm (same scene generator, same pre-roll)."""
 
-    def __init__(self, workload, cfg, n_worlds, dtype, make_scene, threads):
-        init, hulls, _, extras = make_scene(workload, n_worlds, 0)
+    def __init__(self, workload, cfg, n_worlds, dtype, threads):
+        init, hulls, extras = xs.make_scene(workload, n_worlds, 0)
         self.workload, self.cfg, self.threads = workload, cfg, threads
-        self.r = xo.rigid38(init).astype(dtype)
+        self.r = np.ascontiguousarray(init.reshape(-1, 38)).astype(dtype)
         self.hulls, self.extras = hulls, extras
         self.n_worlds = n_worlds
         self.step(cfg["preroll"])  # contact-active state, as on the GPU
@@ -32,7 +33,7 @@ class _Sample:
                            hull_ids=self.extras.get("hull_ids"), joints=self.extras.get("joints"))
 
 
-def time_oracle(workload, cfg, seconds_target, dtype, make_scene):
+def time_oracle(workload, cfg, seconds_target, dtype):
     """Returns (body-substeps/s, cores, sample description, extra dict)."""
     threads = xo.hardware_threads()
     B, S = cfg["bodies"], cfg["substeps"]
@@ -40,7 +41,7 @@ def time_oracle(workload, cfg, seconds_target, dtype, make_scene):
     out = {}
     sample = ""
     for name, dt_ in (("f64", np.float64), ("f32", np.float32)):
-        smp = _Sample(workload, cfg, n_worlds, dt_, make_scene, threads)
+        smp = _Sample(workload, cfg, n_worlds, dt_, threads)
         t0 = time.perf_counter(); smp.step(1); probe = time.perf_counter() - t0
         frames = int(max(1, min(200, (seconds_target / 2) / max(probe, 1e-6))))
         t0 = time.perf_counter(); smp.step(frames); el = time.perf_counter() - t0
@@ -49,21 +50,21 @@ def time_oracle(workload, cfg, seconds_target, dtype, make_scene):
                   f"oracle port, {threads} threads")
     # single thread, f64
     nw1 = max(64 // B, 8) if B <= 16 else 2
-    smp = _Sample(workload, cfg, nw1, np.float64, make_scene, threads)
+    smp = _Sample(workload, cfg, nw1, np.float64, threads)
     f1 = 20 if B <= 16 else 3
     t0 = time.perf_counter(); smp.step(f1, threads=1); el = time.perf_counter() - t0
     one = nw1 * B * S * f1 / el
     return out["f64"], threads, sample, {"value_f32": out["f32"], "value_f64_1thread": one, "precision": "f64 (the reference's)"}
 
 
-def run_reference_arm(workload, cfg, steps, warmup, make_scene):
+def run_reference_arm(workload, cfg, steps, warmup):
     """bench.py --impl reference: each step = one frame of a bounded sample, f64, all host threads."""
     threads = xo.hardware_threads()
     B, S = cfg["bodies"], cfg["substeps"]
     n_worlds = max(threads * 64, 16384 // B) if B <= 16 else threads * 4
     if workload != "c2":
         n_worlds = max(threads * 8, n_worlds // 8)  # multi-body worlds cost ~100x more per body-substep
-    smp = _Sample(workload, cfg, n_worlds, np.float64, make_scene, threads)
+    smp = _Sample(workload, cfg, n_worlds, np.float64, threads)
     for _ in range(warmup):
         smp.step(1)
     t0 = time.perf_counter()

@@ -24,6 +24,61 @@ _L.xo_face_axes_separation_f64.restype = C.c_double
 _L.xo_edge_axes_separation_f32.restype = C.c_float
 _L.xo_edge_axes_separation_f64.restype = C.c_double
 
+# C layouts of the oracle's own entry points (oracle/xo_world_capi.inc: XoPolytope, XoJoint; Rigid = 38 scalars).  They
+# equal the product's records by construction (tests/test_abi.py checks it), but the oracle side declares them itself so
+# that nothing here imports or maps the product library.
+RIGID_DTYPE = np.dtype([("inverse_mass", "f8"), ("inverse_inertia", "f8", (9,)), ("external_force", "f8", (3,)),
+                        ("internal_force", "f8", (3,)), ("external_torque", "f8", (3,)), ("internal_torque", "f8", (3,)),
+                        ("velocity", "f8", (3,)), ("angular_velocity", "f8", (3,)), ("center_of_mass", "f8", (3,)),
+                        ("position", "f8", (3,)), ("rotation", "f8", (4,))])
+JOINT_DTYPE = np.dtype([("body_a", "i4"), ("body_b", "i4"), ("anchor_a", "f8", (3,)), ("anchor_b", "f8", (3,)), ("distance", "f8")])
+
+
+class XoPolytope(C.Structure):
+    _fields_ = [("vertices", C.POINTER(C.c_double)), ("n_vertices", C.c_int32), ("edges", C.POINTER(C.c_int32)),
+                ("n_edges", C.c_int32), ("face_offsets", C.POINTER(C.c_int32)), ("face_indices", C.POINTER(C.c_int32)),
+                ("n_faces", C.c_int32), ("centroid", C.c_double * 3)]
+
+
+class Hull:
+    """Plain holder of a Polytope's arrays (src/geometry.rs:81-93) for the oracle's entry points.  Anything with
+    .vertices / .edges / .faces / .centroid (the product's Polytope included) converts through Hull.of()."""
+
+    def __init__(self, vertices, edges, faces, centroid):
+        self.vertices = np.ascontiguousarray(vertices, dtype=np.float64).reshape(-1, 3)
+        self.edges = np.ascontiguousarray(edges, dtype=np.int32).reshape(-1, 2)
+        self.faces = [list(map(int, f)) for f in faces]
+        self.centroid = np.ascontiguousarray(centroid, dtype=np.float64).reshape(3)
+        self.face_offsets = np.zeros(len(self.faces) + 1, dtype=np.int32)
+        self.face_offsets[1:] = np.cumsum([len(f) for f in self.faces])
+        self.face_indices = np.ascontiguousarray([v for f in self.faces for v in f], dtype=np.int32)
+
+    @staticmethod
+    def of(h) -> "Hull":
+        return h if isinstance(h, Hull) else Hull(h.vertices, h.edges, h.faces, h.centroid)
+
+    @staticmethod
+    def builtin(kind: int) -> "Hull":
+        v, e, fo, fi, c = builtin_hull(kind)
+        return Hull(v, e, [fi[fo[i]:fo[i + 1]].tolist() for i in range(len(fo) - 1)], c)
+
+    def scaled(self, k: float) -> "Hull":  # `f64 * Polytope`, src/geometry.rs:296-307
+        return Hull(k * self.vertices, self.edges, self.faces, k * self.centroid)
+
+    def tuple5(self):
+        return self.vertices, self.edges, self.face_offsets, self.face_indices, self.centroid
+
+    def as_c(self) -> XoPolytope:
+        p = XoPolytope()
+        p.vertices = self.vertices.ctypes.data_as(C.POINTER(C.c_double)); p.n_vertices = len(self.vertices)
+        p.edges = self.edges.ctypes.data_as(C.POINTER(C.c_int32)); p.n_edges = len(self.edges)
+        p.face_offsets = self.face_offsets.ctypes.data_as(C.POINTER(C.c_int32))
+        p.face_indices = self.face_indices.ctypes.data_as(C.POINTER(C.c_int32))
+        p.n_faces = len(self.faces)
+        p.centroid[:] = self.centroid.tolist()
+        return p
+
+
 RIGID_FIELDS = [("inverse_mass", 0, 1), ("inverse_inertia", 1, 9), ("external_force", 10, 3), ("internal_force", 13, 3),
                 ("external_torque", 16, 3), ("internal_torque", 19, 3), ("velocity", 22, 3), ("angular_velocity", 25, 3),
                 ("center_of_mass", 28, 3), ("position", 31, 3), ("rotation", 34, 4)]

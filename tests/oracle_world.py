@@ -4,7 +4,6 @@ import ctypes as C
 import numpy as np
 
 import oracle_lib as xo
-from constraint_solver_b200 import _abi  # record layouts only (PolytopeC / JOINT_DTYPE are plain C layouts)
 
 _L = xo.lib
 _VP = C.c_void_p
@@ -17,27 +16,27 @@ _L.xo_step_worlds_f64.argtypes = [_VP, C.c_int64, C.c_int, _VP, C.c_int, _VP, _V
 
 
 def _hull_array(hulls):
-    """hulls: list of constraint_solver_b200.Polytope (used as plain data holders)."""
-    arr = (_abi.PolytopeC * len(hulls))()
-    for i, h in enumerate(hulls):
+    """hulls: list of oracle_lib.Hull, or of anything with .vertices / .edges / .faces / .centroid (used as data holders)."""
+    keep = [xo.Hull.of(h) for h in hulls]
+    arr = (xo.XoPolytope * len(keep))()
+    for i, h in enumerate(keep):
         arr[i] = h.as_c()
-    return arr
+    return arr, keep
 
 
 def step_worlds(rigids38, B, hulls, dt, substeps, frames, threads=1, hull_ids=None, joints=None, compliance=1e-6,
                 friction=1.0, body_body=True):
-    """step_world on n_worlds worlds of B bodies in place; `hulls` = list of Polytope or a vertex array (cube only)."""
-    from constraint_solver_b200.geometry import Polytope
+    """step_world on n_worlds worlds of B bodies in place; `hulls` = list of hulls (oracle_lib.Hull or Polytope-like)."""
     if not isinstance(hulls, (list, tuple)):
-        hulls = [Polytope.new_cube()]
+        hulls = [xo.Hull.builtin(1)]
     assert rigids38.flags["C_CONTIGUOUS"]
     n_worlds = rigids38.size // (38 * B)
-    harr = _hull_array(hulls)
+    harr, _keep = _hull_array(hulls)
     ids = None if hull_ids is None else np.ascontiguousarray(hull_ids, dtype=np.int32)
     J = 0
     jp = None
     if joints is not None:
-        joints = np.ascontiguousarray(joints, dtype=_abi.JOINT_DTYPE).reshape(n_worlds, -1)
+        joints = np.ascontiguousarray(joints, dtype=xo.JOINT_DTYPE).reshape(n_worlds, -1)
         J = joints.shape[1]
         jp = C.c_void_p(joints.ctypes.data)
     ctr = np.zeros(3, dtype=np.uint64)
@@ -53,7 +52,8 @@ def sat_manifold(fa7, fb7, hull_a, hull_b, dtype=np.float32):
     fa = np.ascontiguousarray(fa7, dtype=dtype); fb = np.ascontiguousarray(fb7, dtype=dtype)
     pts = np.zeros((4, 3), dtype=dtype); tg = np.zeros((4, 3), dtype=dtype)
     feat = C.c_int32(0); inc = C.c_int32(0)
-    ha, hb = hull_a.as_c(), hull_b.as_c()
+    ka, kb = xo.Hull.of(hull_a), xo.Hull.of(hull_b)
+    ha, hb = ka.as_c(), kb.as_c()
     fn = _L.xo_sat_manifold_f32 if dtype == np.float32 else _L.xo_sat_manifold_f64
     n = fn(C.c_void_p(fa.ctypes.data), C.c_void_p(fb.ctypes.data), C.byref(ha), C.byref(hb), C.c_void_p(pts.ctypes.data),
            C.c_void_p(tg.ctypes.data), C.byref(feat), C.byref(inc))
