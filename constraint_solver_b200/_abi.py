@@ -122,6 +122,7 @@ _PROTOTYPES = {
     "xpbd_batch_upload_dynamic_f32": (C.c_int, [_VP, C.c_int64, C.c_int64, _VP]),
     "xpbd_batch_step": (C.c_int, [_VP, C.c_double, C.c_int32, C.c_int32]),
     "xpbd_batch_step_host_f32": (C.c_int, [_VP, C.c_double, C.c_int32, C.c_int32, _VP, _VP]),
+    "xpbd_batch_step_host_rigid": (C.c_int, [_VP, C.c_double, C.c_int32, C.c_int32, _VP, _VP]),
     "xpbd_batch_sync": (C.c_int, [_VP]),
     "xpbd_batch_last_stats": (C.c_int, [_VP, C.POINTER(StepStatsC)]),
     "xpbd_solver_step": (C.c_int, [_VP, C.POINTER(PolytopeC), C.c_double, C.c_int32]),

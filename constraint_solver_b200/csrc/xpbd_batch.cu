@@ -51,6 +51,21 @@ static int forced_world_path() {  // 0 = no override, 1 = fused, 2 = staged
     if (v && !strcmp(v, "staged")) return 2;
     return 0;
 }
+int rigid_io_before(xpbd_batch* b, int64_t g0, int64_t n, cudaStream_t st) {
+    if (!b->io_rigid_in || n <= 0) return XPBD_OK;
+    double* dst = b->d_rigid_stage + 38 * g0;
+    XPBD_CUDA_TRY(cudaMemcpyAsync(dst, b->io_rigid_in + g0, (size_t)n * sizeof(xpbd_rigid), cudaMemcpyHostToDevice, st));
+    launch_aos64_to_soa(dst, b->arrays, g0, n, st);
+    return XPBD_OK;
+}
+int rigid_io_after(xpbd_batch* b, int64_t g0, int64_t n, cudaStream_t st) {
+    if (!b->io_rigid_out || n <= 0) return XPBD_OK;
+    double* src = b->d_rigid_stage + 38 * g0;
+    if (b->rigid_stage_valid) launch_soa_dyn_to_aos64(b->arrays, src, g0, n, st);  // constants stay the caller's f64 bits
+    else launch_soa_to_aos64(b->arrays, src, g0, n, st);
+    XPBD_CUDA_TRY(cudaMemcpyAsync(b->io_rigid_out + g0, src, (size_t)n * sizeof(xpbd_rigid), cudaMemcpyDeviceToHost, st));
+    return XPBD_OK;
+}
 bool world_path_is_staged(const xpbd_batch* b) {
     const int forced = forced_world_path();
     if (forced) return forced == 2;
@@ -147,6 +162,7 @@ int xpbd_batch_destroy(xpbd_batch* b) {
         if (b->stage_free[s]) cudaEventDestroy(b->stage_free[s]);
     }
     if (b->d_dyn_stage) cudaFree(b->d_dyn_stage);
+    if (b->d_rigid_stage) cudaFree(b->d_rigid_stage);
     for (int s = 0; s < 2; ++s)
         if (b->d_order[s]) cudaFree(b->d_order[s]);
     if (b->d_contact_count) cudaFree(b->d_contact_count);
@@ -344,7 +360,8 @@ int xpbd_batch_upload_dynamic_f32(xpbd_batch* b, int64_t first_world, int64_t n_
     return XPBD_OK;  // ordered before any later launch on the batch stream
 }
 
-static int step_common(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_frames, const float* in, float* out);
+static int step_common(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_frames, const float* in, float* out,
+                       const xpbd_rigid* rin = nullptr, xpbd_rigid* rout = nullptr);
 
 int xpbd_batch_step(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_frames) {
     return step_common(b, dt, substep_count, n_frames, nullptr, nullptr);
@@ -354,13 +371,23 @@ int xpbd_batch_step_host_f32(xpbd_batch* b, double dt, int32_t substep_count, in
     return step_common(b, dt, substep_count, n_frames, in, out);
 }
 
-static int step_common(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_frames, const float* in, float* out) {
+int xpbd_batch_step_host_rigid(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_frames, const xpbd_rigid* in,
+                               xpbd_rigid* out) {
+    return step_common(b, dt, substep_count, n_frames, nullptr, nullptr, in, out);
+}
+
+static int step_common(xpbd_batch* b, double dt, int32_t substep_count, int32_t n_frames, const float* in, float* out,
+                       const xpbd_rigid* rin, xpbd_rigid* rout) {
     if (int rc = check_batch(b)) return rc;
     if (substep_count <= 0 || n_frames <= 0) return fail(XPBD_ERR_INVALID, "substep_count and n_frames must be positive");
     if (!(dt > 0.0) || !std::isfinite(dt)) return fail(XPBD_ERR_INVALID, "dt must be positive and finite");
     if (int rc = bind_device(b)) return rc;
     if (int rc = finalize_hulls(b)) return rc;
     if (in || out) { if (int rc = ensure_dyn_stage(b)) return rc; }
+    if ((rin || rout) && !b->d_rigid_stage) {
+        XPBD_CUDA_TRY(cudaMalloc(&b->d_rigid_stage, (size_t)b->n_bodies * sizeof(xpbd_rigid)));
+        b->rigid_stage_valid = false;
+    }
     XPBD_CUDA_TRY(cudaEventRecord(b->ev_start, b->stream));
     XPBD_CUDA_TRY(cudaMemsetAsync(b->d_counters, 0, kBatchCounters * sizeof(unsigned long long), b->stream));
     b->stage_timed = false;
@@ -370,6 +397,11 @@ static int step_common(xpbd_batch* b, double dt, int32_t substep_count, int32_t 
     // pointers; every other path copies the whole batch on the batch stream around its kernels.
     b->io_in = in;
     b->io_out = out;
+    b->io_rigid_in = rin;
+    b->io_rigid_out = rout;
+    const bool per_range_io = world_path && staged_takes_host_buffers(b);
+    if (rin) b->rigid_stage_valid = true;  // the staging mirror holds every body's record once this call's uploads ran
+    if (!per_range_io) { if (int rc = rigid_io_before(b, 0, b->n_bodies, b->stream)) return rc; }
     if (b->io_in && !(world_path && staged_takes_host_buffers(b))) {
         XPBD_CUDA_TRY(cudaMemcpyAsync(b->d_dyn_stage, b->io_in, (size_t)b->n_bodies * 13 * sizeof(float), cudaMemcpyHostToDevice, b->stream));
         launch_dyn_unpack(b->d_dyn_stage, b->arrays, 0, b->n_bodies, b->stream);
@@ -377,7 +409,10 @@ static int step_common(xpbd_batch* b, double dt, int32_t substep_count, int32_t 
     }
     int rc = world_path ? step_world(b, (float)dt, substep_count, n_frames)
                         : step_single(b, (float)dt, substep_count, n_frames);
-    if (rc != XPBD_OK) { b->io_in = nullptr; b->io_out = nullptr; return rc; }
+    if (rc != XPBD_OK) { b->io_in = nullptr; b->io_out = nullptr; b->io_rigid_in = nullptr; b->io_rigid_out = nullptr; return rc; }
+    if (!per_range_io || b->last.sub_batches <= 1) { if (int rc2 = rigid_io_after(b, 0, b->n_bodies, b->stream)) return rc2; }
+    b->io_rigid_in = nullptr;
+    b->io_rigid_out = nullptr;
     if (b->io_out) {  // not consumed per range
         launch_dyn_pack(b->arrays, b->d_dyn_stage, 0, b->n_bodies, b->stream);
         XPBD_CUDA_TRY(cudaMemcpyAsync(b->io_out, b->d_dyn_stage, (size_t)b->n_bodies * 13 * sizeof(float), cudaMemcpyDeviceToHost, b->stream));

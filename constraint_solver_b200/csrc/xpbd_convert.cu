@@ -46,6 +46,20 @@ __global__ void soa_to_aos64_kernel(BodyArrays s, double* __restrict__ aos, int6
     r[27] = s.dynD[g];
 }
 
+// Only the 13 values a step mutates (velocity, angular_velocity, position, rotation), widened into AoS f64 records whose
+// other 25 fields are left as they are: the caller's f64 constants survive a round trip bit for bit.
+__global__ void soa_dyn_to_aos64_kernel(BodyArrays s, double* __restrict__ aos, int64_t first, int64_t n) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double* r = aos + 38 * i;
+    int64_t g = first + i;
+    float4 a = s.dynA[g], b = s.dynB[g], c = s.dynC[g];
+    r[31] = a.x; r[32] = a.y; r[33] = a.z; r[22] = a.w;
+    r[23] = b.x; r[24] = b.y; r[25] = b.z; r[26] = b.w;
+    r[34] = c.x; r[35] = c.y; r[36] = c.z; r[37] = c.w;
+    r[27] = s.dynD[g];
+}
+
 // Replicate the bodies of one world (already converted at g in [0, B)) into all worlds.
 __global__ void broadcast_world_kernel(BodyArrays s, int bodies_per_world, int64_t n_bodies) {
     int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -126,6 +140,9 @@ void launch_aos64_to_soa(const double* aos, const BodyArrays& s, int64_t first, 
 }
 void launch_soa_to_aos64(const BodyArrays& s, double* aos, int64_t first, int64_t n, cudaStream_t st) {
     if (n > 0) soa_to_aos64_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s, aos, first, n);
+}
+void launch_soa_dyn_to_aos64(const BodyArrays& s, double* aos, int64_t first, int64_t n, cudaStream_t st) {
+    if (n > 0) soa_dyn_to_aos64_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s, aos, first, n);
 }
 void launch_broadcast_world(const BodyArrays& s, int bodies_per_world, int64_t n_bodies, cudaStream_t st) {
     if (n_bodies > 0) broadcast_world_kernel<<<(unsigned)((n_bodies + 255) / 256), 256, 0, st>>>(s, bodies_per_world, n_bodies);

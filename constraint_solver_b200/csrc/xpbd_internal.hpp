@@ -59,6 +59,7 @@ struct DeviceHulls {
 // ---- kernel launchers (defined in the .cu files) --------------------------------------------
 void launch_aos64_to_soa(const double* aos, const BodyArrays& s, int64_t first, int64_t n, cudaStream_t st);
 void launch_soa_to_aos64(const BodyArrays& s, double* aos, int64_t first, int64_t n, cudaStream_t st);
+void launch_soa_dyn_to_aos64(const BodyArrays& s, double* aos, int64_t first, int64_t n, cudaStream_t st);
 void launch_broadcast_world(const BodyArrays& s, int bodies_per_world, int64_t n_bodies, cudaStream_t st);
 void launch_dyn_pack(const BodyArrays& s, float* out, int64_t first, int64_t n, cudaStream_t st);
 void launch_dyn_unpack(const float* in, const BodyArrays& s, int64_t first, int64_t n, cudaStream_t st);
@@ -125,6 +126,13 @@ struct xpbd_batch {
     // xpbd_batch_step_host_f32: host buffers of the step call in flight (packed dynamic state, 13 floats per body)
     const float* io_in = nullptr;
     float* io_out = nullptr;
+    // xpbd_batch_step_host_rigid: the same with the reference's own records (xpbd_rigid, 38 f64 per body).  d_rigid_stage
+    // mirrors the caller's records on the device (n_bodies x 304 B); rigid_stage_valid = it holds every body's constants
+    // as uploaded, so a download only has to refresh the 13 dynamic values.
+    const xpbd_rigid* io_rigid_in = nullptr;
+    xpbd_rigid* io_rigid_out = nullptr;
+    double* d_rigid_stage = nullptr;
+    bool rigid_stage_valid = false;
 };
 
 namespace xpbd {
@@ -134,6 +142,10 @@ int step_world_fused(xpbd_batch* b, float frame_dt, int substeps, int n_frames);
 int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames);  // xpbd_staged.cu
 int step_world(xpbd_batch* b, float frame_dt, int substeps, int n_frames);         // picks one of the two
 void release_world_scratch(xpbd_batch* b);
+// Host-record legs of a step call for bodies [g0, g0 + n) on `st` (xpbd_batch_step_host_rigid): H2D + conversion before the
+// kernels, conversion + D2H after them.  Used per world range by the staged pipeline, for the whole batch otherwise.
+int rigid_io_before(xpbd_batch* b, int64_t g0, int64_t n, cudaStream_t st);
+int rigid_io_after(xpbd_batch* b, int64_t g0, int64_t n, cudaStream_t st);
 // true when the next multi-body step call will run the staged pipeline on several world ranges (which then move
 // b->io_in / b->io_out per range, on the range streams)
 bool staged_takes_host_buffers(const xpbd_batch* b);

@@ -15,9 +15,10 @@
 //                   vertex index) for the accesses whose vertex index is hull data (edge end points, witnesses), and
 //                   the per-thread survivor masks of the cull, 12 bits per edge of A.
 // No two threads share scratch, so the kernel has no barrier after the hull table is staged.
-// kFuse: the manifold stage (Sutherland-Hodgman clipping -> the pair's <= 4 contacts) runs as the epilogue of the same
-// thread, reusing the scratch column, instead of as a kernel of its own (one launch, one work-list pass and the
-// latency-bound tail of stage_manifold_kernel less per substep).
+// (Measured and rejected: running the manifold stage as the epilogue of this thread, with the clip polygons in the same
+// scratch column.  SAT + manifold as one kernel took 0.72 ms against 0.48 + 0.20 ms as two: the executed code grows from
+// ~2 500 to ~5 000 instructions, "no instruction" stalls rise from 0.16 to 0.55 per issue and issue utilisation drops
+// from 75 % to 61 % — instruction cache.)
 #pragma once
 
 namespace xpbd {
@@ -38,31 +39,13 @@ XD float sqrt_approx(float x) {
     return r;
 }
 
-// The thread's scratch: one COLUMN of float4 slots, [slot][thread] (a thread only ever touches its own column, so
-// different phases may reuse the slots without any synchronisation).
+// The thread's scratch: one COLUMN of float4 slots, [slot][thread]; a thread only ever touches its own column.
 struct SatThreadScratch {
     float4* col;  // already offset by the thread index: slots 0..7 A's vertices, 8..15 B's, 16..18 survivor masks
     XD V3 vert(int v) const { const float4 x = col[v * kSatThreadBlock]; return v3(x.x, x.y, x.z); }
     XD void set_vert(int v, float4 x) const { col[v * kSatThreadBlock] = x; }
     XD uint32_t* mask(int ia) const { return reinterpret_cast<uint32_t*>(col + (16 + (ia >> 2)) * kSatThreadBlock) + (ia & 3); }
 };
-// Clip scratch of the manifold epilogue (interface of ClipShared, 8 entries per buffer — cube-shaped hulls with quad faces),
-// in the same column: the two polygon buffers take slots 0..15 (one LDS.128 / STS.128 per point), the depths slots 16..17.
-// The vertices and masks that lived there are dead by then; face_manifold reads the hull vertices from global memory.
-struct ClipColumns {
-    float4* col;
-    bool over = false;
-    XD V3 get(int w, int k) const { k = k < 8 ? k : 7; const float4 x = col[(w * 8 + k) * kSatThreadBlock]; return v3(x.x, x.y, x.z); }
-    XD void set(int w, int k, V3 v) {
-        if (k >= 8) { over = true; return; }
-        col[(w * 8 + k) * kSatThreadBlock] = make_float4(v.x, v.y, v.z, 0.0f);
-    }
-    XD float depth(int k) const { k = k < 8 ? k : 7; return reinterpret_cast<const float*>(col + (16 + (k >> 2)) * kSatThreadBlock)[k & 3]; }
-    XD void set_depth(int k, float d) { if (k < 8) reinterpret_cast<float*>(col + (16 + (k >> 2)) * kSatThreadBlock)[k & 3] = d; }
-    XD bool overflowed() const { return over; }
-    XD void reset() { over = false; }
-};
-
 // face_axes_separation (src/collision.rs:123-149) of a 6-face hull against 8 vertices `WO` of the other hull; L = those
 // vertices in the face hull's local space (kept by the caller for the witnesses).
 XD void face_query_thread(const float4* planes, const Fr& Finv, const V3 (&WO)[8], V3 (&L)[8], float& out_d, int& out_face) {
@@ -109,7 +92,7 @@ XD int2 witness_vertices_thread(float4 plane, const V3 (&L)[8]) {
     return make_int2(v1, v2);
 }
 
-template <bool kCull, bool kFuse>
+template <bool kCull>
 XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, const SatThreadScratch& S) {
     const int B = P.B, maxV = P.S.maxV;
     const int64_t world = d.w;
@@ -227,13 +210,9 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
 done:
     P.S.pairs[d.x].y = pf.feature;
     P.S.pairs[d.x].z = pf.index;
-    if (kFuse) {  // stage 3 as the epilogue: clipping -> the pair's contacts (see manifold_candidate)
-        ClipColumns clip{S.col};
-        manifold_candidate(P, T, (uint32_t)d.x, make_int4(d.y, pf.feature, pf.index, 0), clip);
-    }
 }
 
-template <bool kCull, bool kFuse>
+template <bool kCull>
 __global__ void __launch_bounds__(kSatThreadBlock, XPBD_SAT_THREAD_MIN_BLOCKS) stage_sat_thread_kernel(StagedParams P) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ __align__(8) uint64_t bar;
@@ -243,7 +222,7 @@ __global__ void __launch_bounds__(kSatThreadBlock, XPBD_SAT_THREAD_MIN_BLOCKS) s
     S.col = reinterpret_cast<float4*>(smem + P.hull_blob_bytes / 4) + threadIdx.x;
     const unsigned count = *P.S.work_count;
     for (unsigned it = blockIdx.x * blockDim.x + threadIdx.x; it < count; it += gridDim.x * blockDim.x)
-        sat_thread_candidate<kCull, kFuse>(P, T, P.S.worklist[it], S);
+        sat_thread_candidate<kCull>(P, T, P.S.worklist[it], S);
 }
 
 }  // namespace xpbd

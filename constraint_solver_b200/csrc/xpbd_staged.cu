@@ -458,8 +458,7 @@ __global__ void __launch_bounds__(256, XPBD_SAT_MIN_BLOCKS) stage_sat_cubes_kern
 }
 
 // Manifold of one candidate whose SAT result is in pr (.x = i | j << 16, .y = feature, .z = index): clipping -> <= 4 fresh
-// contacts in the pair's slot, count in pairs[slot].w.  Shared by stage_manifold_kernel (thread per candidate) and by the
-// thread-per-candidate SAT kernel, which runs it as its epilogue.
+// contacts in the pair's slot, count in pairs[slot].w.
 template <class Clip>
 XD void manifold_candidate(const StagedParams& P, const HullTable& T, uint32_t slot, int4 pr, Clip& clip) {
     const int B = P.B, maxV = P.S.maxV;
@@ -739,7 +738,6 @@ struct StagedState {
     int B = 0;
     int grid_prepare = 0, grid_sat = 0, grid_manifold = 0;
     size_t smem_prepare = 0, smem_sat = 0, smem_manifold = 0;
-    bool fuse_manifold = false;   // sat_fn also writes the manifolds (thread-per-candidate kernel): no stage_manifold launch
     int sat_threads = 256;        // block size of sat_fn
     int sat_cands_per_block = 8;  // candidates one block of sat_fn takes per grid-stride round
     int warps_prepare = 8;
@@ -882,10 +880,7 @@ static int build_staged(xpbd_batch* b, StagedState* st) {
                 st->sat_fn = cull ? stage_sat_cubes_kernel<true> : stage_sat_cubes_kernel<false>;
                 st->sat_cands_per_block = 16;
             } else {
-                const char* fz = std::getenv("XPBD_SAT_FUSE");  // "0": keep stage_manifold as a kernel of its own (A/B runs)
-                st->fuse_manifold = !(fz && fz[0] == '0') && H.max_face_verts <= 4;
-                st->sat_fn = st->fuse_manifold ? (cull ? stage_sat_thread_kernel<true, true> : stage_sat_thread_kernel<false, true>)
-                                               : (cull ? stage_sat_thread_kernel<true, false> : stage_sat_thread_kernel<false, false>);
+                st->sat_fn = cull ? stage_sat_thread_kernel<true> : stage_sat_thread_kernel<false>;
                 st->sat_threads = kSatThreadBlock;
                 st->sat_cands_per_block = kSatThreadBlock;
                 st->smem_sat = sat_thread_smem_bytes(H.bytes);
@@ -1025,6 +1020,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
             Q.counters = st->d_range_counters + 4 * k;
             if (fork) XPBD_CUDA_TRY(cudaStreamWaitEvent(stream, st->ev_fork, 0));
             XPBD_CUDA_TRY(cudaMemsetAsync(Q.counters, 0, 4 * sizeof(unsigned long long), stream));
+            if (int rc = rigid_io_before(b, g0, nw * B, stream)) return rc;  // xpbd_batch_step_host_rigid, same per-range pipelining
             if (b->io_in) {  // xpbd_batch_step_host_f32: this range's state from the host, under the other ranges' kernels
                 XPBD_CUDA_TRY(cudaMemcpyAsync(b->d_dyn_stage + 13 * g0, b->io_in + 13 * g0, (size_t)(nw * B) * 13 * sizeof(float), cudaMemcpyHostToDevice, stream));
                 launch_dyn_unpack(b->d_dyn_stage + 13 * g0, b->arrays, g0, nw * B, stream);
@@ -1045,7 +1041,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
             if (timed) cudaEventRecord(b->ev_stage[1], stream);
             if (P.body_body) st->sat_fn<<<grid_sat, st->sat_threads, st->smem_sat, stream>>>(Q);
             if (timed) cudaEventRecord(b->ev_stage[2], stream);
-            if (P.body_body && !st->fuse_manifold) st->manifold_fn<<<grid_manifold, kManifoldThreads, st->smem_manifold, stream>>>(Q);
+            if (P.body_body) st->manifold_fn<<<grid_manifold, kManifoldThreads, st->smem_manifold, stream>>>(Q);
             if (timed) cudaEventRecord(b->ev_stage[3], stream);
             stage_solve_kernel<<<grid_solve, 128, 0, stream>>>(Q);
             if (timed) cudaEventRecord(b->ev_stage[4], stream);
@@ -1054,6 +1050,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
             launch_dyn_pack(b->arrays, b->d_dyn_stage + 13 * g0, g0, nw * B, stream);
             XPBD_CUDA_TRY(cudaMemcpyAsync(b->io_out + 13 * g0, b->d_dyn_stage + 13 * g0, (size_t)(nw * B) * 13 * sizeof(float), cudaMemcpyDeviceToHost, stream));
         }
+        if (n_sub > 1) { if (int rc = rigid_io_after(b, g0, nw * B, stream)) return rc; }
         if (n_sub > 1) {
             XPBD_CUDA_TRY(cudaMemcpyAsync(st->h_range_counters + 4 * k, Q.counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
             XPBD_CUDA_TRY(cudaEventRecord(st->sub_done[k], stream));
@@ -1061,11 +1058,11 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
         }
     }
     b->fork_needed = false;
-    if (n_sub > 1) { b->io_in = nullptr; b->io_out = nullptr; }  // consumed per range
+    if (n_sub > 1) { b->io_in = nullptr; b->io_out = nullptr; b->io_rigid_in = nullptr; b->io_rigid_out = nullptr; }  // consumed per range
     b->last.sub_batches = n_sub;
     b->stage_timed = true;
     XPBD_CUDA_TRY(cudaGetLastError());
-    b->last.kernel_launches = n_sub * total * (P.body_body ? (st->fuse_manifold ? 3 : 4) : 2);
+    b->last.kernel_launches = n_sub * total * (P.body_body ? 4 : 2);
     return XPBD_OK;
 }
 
@@ -1158,7 +1155,7 @@ extern "C" int xpbd_sat_feature_batch(const xpbd_frame* fa, const xpbd_frame* fb
     size_t smem = dev.bytes + 8 * (size_t)sat_words_per_warp(maxV) * 4;
     if (schedule == 0) fn = cull ? stage_sat_kernel<true> : stage_sat_kernel<false>;
     else if (schedule == 1) fn = cull ? stage_sat_cubes_kernel<true> : stage_sat_cubes_kernel<false>;
-    else { fn = cull ? stage_sat_thread_kernel<true, false> : stage_sat_thread_kernel<false, false>; threads = kSatThreadBlock; smem = sat_thread_smem_bytes(dev.bytes); }
+    else { fn = cull ? stage_sat_thread_kernel<true> : stage_sat_thread_kernel<false>; threads = kSatThreadBlock; smem = sat_thread_smem_bytes(dev.bytes); }
     XPBD_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 1, n_sm = 148, devid = 0;
     XPBD_CUDA_TRY(cudaGetDevice(&devid));

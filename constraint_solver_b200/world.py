@@ -182,6 +182,22 @@ class Worlds:
         self.integrate_host_ptr(dt, substep_count, n_frames, 0 if dyn_in is None else dyn_in.ctypes.data, out.ctypes.data)
         return out
 
+    def integrate_host_rigid_ptr(self, dt: float, substep_count: int, n_frames: int, in_ptr: int, out_ptr: int, sync: bool = True) -> None:
+        """World::integrate for callers holding the reference's own f64 records (xpbd_rigid, 304 B per body) in host memory:
+        upload (0 = keep the device state), step, write the records back (0 = none) — xpbd_batch_step_host_rigid."""
+        _abi.check(self._lib.xpbd_batch_step_host_rigid(self._h, float(dt), int(substep_count), int(n_frames),
+                                                        C.c_void_p(in_ptr or None), C.c_void_p(out_ptr or None)))
+        if sync:
+            self.sync()
+
+    def integrate_host_rigid(self, rigids: np.ndarray, dt: float, substep_count: int = SUBSTEPS, n_frames: int = 1) -> np.ndarray:
+        """Numpy form: steps the given records (RIGID_DTYPE, n_worlds x bodies_per_world) and returns the new records."""
+        rec = np.ascontiguousarray(rigids, dtype=_abi.RIGID_DTYPE)
+        assert rec.size == self.n_bodies
+        out = np.empty_like(rec)
+        self.integrate_host_rigid_ptr(dt, substep_count, n_frames, rec.ctypes.data, out.ctypes.data)
+        return out
+
     def sync(self) -> None:
         _abi.check(self._lib.xpbd_batch_sync(self._h))
 

@@ -190,6 +190,13 @@ int xpbd_batch_step(xpbd_batch* batch, double dt, int32_t substep_count, int32_t
  * serialises the copies. */
 int xpbd_batch_step_host_f32(xpbd_batch* batch, double dt, int32_t substep_count, int32_t n_frames, const float* in,
                              float* out);
+/* The same for callers holding the reference's own records (`Vec<Rigid>` / `World`, src/rigid.rs:7-50, src/app.rs:204-215:
+ * 304 bytes per body): uploads `in` (all 38 fields, f64 -> f32; NULL = keep the device state), steps, and writes the records
+ * into `out` (NULL = none; may equal `in`): the 13 values solver::step mutates at fp32 precision, every other field exactly
+ * as it was uploaded through this call (the caller's f64 bits are not rounded; without an earlier `in` they are the device's
+ * fp32 values).  Asynchronous like xpbd_batch_step_host_f32; copies are pipelined per world range. */
+int xpbd_batch_step_host_rigid(xpbd_batch* batch, double dt, int32_t substep_count, int32_t n_frames, const xpbd_rigid* in,
+                               xpbd_rigid* out);
 int xpbd_batch_sync(xpbd_batch* batch);
 /* Valid after xpbd_batch_sync. */
 int xpbd_batch_last_stats(xpbd_batch* batch, xpbd_step_stats* out);

@@ -17,6 +17,8 @@
 #include <cstring>
 #include <limits>
 
+#include "xo_count.hpp"
+
 namespace xo {
 
 // ---- cgmath::Vector3 -------------------------------------------------------------------
@@ -46,7 +48,7 @@ template <class S> inline Vec3<S> cross(Vec3<S> a, Vec3<S> b) {
     return {(a.y * b.z) - (a.z * b.y), (a.z * b.x) - (a.x * b.z), (a.x * b.y) - (a.y * b.x)};
 }
 template <class S> inline S magnitude2(Vec3<S> a) { return dot(a, a); }
-template <class S> inline S magnitude(Vec3<S> a) { return std::sqrt(magnitude2(a)); }
+template <class S> inline S magnitude(Vec3<S> a) { return sqrt_s(magnitude2(a)); }
 // normalize = normalize_to(1) = self * (1 / magnitude)
 template <class S> inline Vec3<S> normalize(Vec3<S> a) { return a * (S(1) / magnitude(a)); }
 // project_on(other) = other * (self.dot(other) / other.magnitude2())
@@ -85,7 +87,7 @@ template <class S> inline Vec3<S> operator*(Quat<S> q, Vec3<S> r) {
 }
 // InnerSpace for Quaternion: dot = s*s' + v.dot(v')
 template <class S> inline S dot(Quat<S> a, Quat<S> b) { return a.s * b.s + dot(a.v, b.v); }
-template <class S> inline S magnitude(Quat<S> q) { return std::sqrt(dot(q, q)); }
+template <class S> inline S magnitude(Quat<S> q) { return sqrt_s(dot(q, q)); }
 template <class S> inline Quat<S> normalize(Quat<S> q) { return q * (S(1) / magnitude(q)); }
 
 // Quaternion::from(Euler{x,y,z}) with angles in radians (cgmath 0.18 quaternion.rs)

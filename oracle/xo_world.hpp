@@ -91,6 +91,29 @@ struct Hull {
     }
 };
 
+// Phases of a substep, for the flop bookkeeping of the Counted<T> instantiation (xo_count.hpp).
+enum Phase : int { kPhIntegrate = 0, kPhGround, kPhBroadphase, kPhFaceQueries, kPhEdgeQuery, kPhManifold, kPhSweep, kPhDerive,
+                   kPhVelocity, kPhCount };
+template <class S>
+struct StepCounters {
+    uint64_t constraints = 0, pairs_tested = 0, manifolds = 0, active_contacts = 0;
+    uint64_t flops[kPhCount][4] = {};  // add, mul, div, sqrt per phase (all zero unless S = Counted<T>)
+};
+// Adds the flops performed during its lifetime to one phase of the counters (compiles to nothing for plain scalars).
+template <class S>
+struct PhaseScope {
+    StepCounters<S>* c;
+    int phase;
+    FlopCounters t0;
+    PhaseScope(StepCounters<S>* c_, int phase_) : c(c_), phase(phase_), t0(FlopProbe<S>::now()) {}
+    ~PhaseScope() {
+        if (!c) return;
+        const FlopCounters t1 = FlopProbe<S>::now();
+        c->flops[phase][0] += t1.add - t0.add; c->flops[phase][1] += t1.mul - t0.mul;
+        c->flops[phase][2] += t1.div - t0.div; c->flops[phase][3] += t1.sqrt - t0.sqrt;
+    }
+};
+
 // ---- narrowphase ---------------------------------------------------------------------------
 enum Feature : int { kNone = 0, kFaceA = 1, kFaceB = 2, kEdgeEdge = 3 };
 
@@ -215,14 +238,23 @@ void edge_manifold(Vec3<S> p1, Vec3<S> q1, Vec3<S> p2, Vec3<S> q2, Manifold<S>& 
 
 // The finished `sat`: contact manifold between body A (frames.0, hulls.0) and body B.
 template <class S>
-Manifold<S> sat_manifold(Frame<S> fa, Frame<S> fb, const Hull<S>& ha, const Hull<S>& hb) {
+Manifold<S> sat_manifold(Frame<S> fa, Frame<S> fb, const Hull<S>& ha, const Hull<S>& hb, StepCounters<S>* ctr = nullptr) {
     Manifold<S> m;
-    FaceQuery<S> qa = face_axes_separation(fa, fb, ha.poly, hb.poly);
-    if (qa.distance >= S(0)) return m;
-    FaceQuery<S> qb = face_axes_separation(fb, fa, hb.poly, ha.poly);
-    if (qb.distance >= S(0)) return m;
-    EdgeQuery<S> qe = edge_axes_separation(fa, fb, ha.poly, hb.poly);
-    if (qe.distance >= S(0)) return m;
+    FaceQuery<S> qa, qb;
+    EdgeQuery<S> qe;
+    {
+        PhaseScope<S> ph(ctr, kPhFaceQueries);
+        qa = face_axes_separation(fa, fb, ha.poly, hb.poly);
+        if (qa.distance >= S(0)) return m;
+        qb = face_axes_separation(fb, fa, hb.poly, ha.poly);
+        if (qb.distance >= S(0)) return m;
+    }
+    {
+        PhaseScope<S> ph(ctr, kPhEdgeQuery);
+        qe = edge_axes_separation(fa, fb, ha.poly, hb.poly);
+        if (qe.distance >= S(0)) return m;
+    }
+    PhaseScope<S> ph(ctr, kPhManifold);
     S face_max = qa.distance > qb.distance ? qa.distance : qb.distance;
     if (qe.edge0 >= 0 && qe.distance > Tuning<S>::rel_edge() * face_max + Tuning<S>::abs_tol()) {
         m.feature = kEdgeEdge;
@@ -266,16 +298,17 @@ struct WorldState {
 };
 
 template <class S>
-struct StepCounters { uint64_t constraints = 0, pairs_tested = 0, manifolds = 0, active_contacts = 0; };
-
-template <class S>
 void generate_constraints(const WorldState<S>& w, const std::vector<Hull<S>>& hulls, const std::vector<Frame<S>>& past,
                           const WorldParams<S>& prm, std::vector<Constraint2<S>>& out, StepCounters<S>* ctr) {
     const int B = (int)w.bodies.size();
     std::vector<Frame<S>> frames((size_t)B);
-    for (int b = 0; b < B; ++b) frames[(size_t)b] = w.bodies[(size_t)b].frame();
+    {
+        PhaseScope<S> ph(ctr, kPhIntegrate);
+        for (int b = 0; b < B; ++b) frames[(size_t)b] = w.bodies[(size_t)b].frame();
+    }
     // 1. ground, body-major, hull vertex order (src/collision.rs:13-35 per body)
     for (int b = 0; b < B; ++b) {
+        PhaseScope<S> ph(ctr, kPhGround);
         const Rigid<S>& rigid = w.bodies[(size_t)b];
         for (const Vec3<S>& vertex : hulls[(size_t)w.hull_of[(size_t)b]].poly.vertices) {
             Vec3<S> position = rigid.frame() * vertex;
@@ -298,13 +331,17 @@ void generate_constraints(const WorldState<S>& w, const std::vector<Hull<S>>& hu
             for (int j = i + 1; j < B; ++j) {
                 const Hull<S>& hi = hulls[(size_t)w.hull_of[(size_t)i]];
                 const Hull<S>& hj = hulls[(size_t)w.hull_of[(size_t)j]];
-                Vec3<S> ci = frames[(size_t)i] * hi.poly.centroid, cj = frames[(size_t)j] * hj.poly.centroid;
-                S rsum = hi.radius + hj.radius;
-                if (magnitude2(cj - ci) > rsum * rsum) continue;  // bounding spheres
+                {
+                    PhaseScope<S> ph(ctr, kPhBroadphase);
+                    Vec3<S> ci = frames[(size_t)i] * hi.poly.centroid, cj = frames[(size_t)j] * hj.poly.centroid;
+                    S rsum = hi.radius + hj.radius;
+                    if (magnitude2(cj - ci) > rsum * rsum) continue;  // bounding spheres
+                }
                 if (ctr) ctr->pairs_tested++;
-                Manifold<S> m = sat_manifold(frames[(size_t)i], frames[(size_t)j], hi, hj);
+                Manifold<S> m = sat_manifold(frames[(size_t)i], frames[(size_t)j], hi, hj, ctr);
                 if (m.count && ctr) ctr->manifolds++;
                 int inc = m.incident == 0 ? i : j, oth = m.incident == 0 ? j : i;
+                PhaseScope<S> ph(ctr, kPhManifold);
                 for (int k = 0; k < m.count; ++k) {
                     Constraint2<S> c;
                     if (contact_constraint(inc, oth, frames[(size_t)inc], frames[(size_t)oth], m.point[(size_t)k],
@@ -415,17 +452,20 @@ void step_world(WorldState<S>& w, const std::vector<Hull<S>>& hulls, const World
     std::vector<Constraint2<S>> cs;
     std::vector<char> active;
     for (size_t k = 0; k < substep_count; ++k) {
-        for (size_t b = 0; b < B; ++b) {
-            past_pos[b] = w.bodies[b].position;
-            past_rot[b] = w.bodies[b].rotation;
-            past[b] = w.bodies[b].frame();
-            w.bodies[b].integrate(dt);
+        {
+            PhaseScope<S> ph(ctr, kPhIntegrate);
+            for (size_t b = 0; b < B; ++b) {
+                past_pos[b] = w.bodies[b].position;
+                past_rot[b] = w.bodies[b].rotation;
+                past[b] = w.bodies[b].frame();
+                w.bodies[b].integrate(dt);
+            }
         }
         cs.clear();
         generate_constraints(w, hulls, past, prm, cs, ctr);
-        sweep(w, cs, compliance, active);
-        for (size_t b = 0; b < B; ++b) w.bodies[b].derive(past_pos[b], past_rot[b], dt);
-        solve_velocities(w, cs, active, prm.friction);
+        { PhaseScope<S> ph(ctr, kPhSweep); sweep(w, cs, compliance, active); }
+        { PhaseScope<S> ph(ctr, kPhDerive); for (size_t b = 0; b < B; ++b) w.bodies[b].derive(past_pos[b], past_rot[b], dt); }
+        { PhaseScope<S> ph(ctr, kPhVelocity); solve_velocities(w, cs, active, prm.friction); }
         if (ctr) {
             ctr->constraints += cs.size();
             for (char a : active) ctr->active_contacts += (uint64_t)a;

@@ -73,3 +73,49 @@ def run_reference_arm(workload, cfg, steps, warmup):
     el = time.perf_counter() - t0
     return {"value": n_worlds * B * S * steps / el, "ms_per_step": el / steps * 1e3, "cores": threads,
             "sample": f"{n_worlds} worlds x {B} bodies per step (bounded sample of the workload), f64 oracle port, {threads} threads"}
+
+
+def algorithmic_flops(workload, cfg, n_worlds=None):
+    """Algorithmic flops of the specification per body-substep, by phase (add = mul = div = sqrt = 1, SURVEY.md section 8
+    row D): the oracle instantiated with its counting scalar (oracle/xo_count.hpp) steps a small sample of the workload
+    for one frame after the same pre-roll.  The reference's face / edge queries are counted as written (brute force)."""
+    import oracle_world as xw
+    threads = xo.hardware_threads()
+    B, S = cfg["bodies"], cfg["substeps"]
+    n_worlds = n_worlds or (16 if B <= 16 else 2)
+    smp = _Sample(workload, cfg, n_worlds, np.float32, threads)
+    c = xw.count_flops_worlds(smp.r, B, list(smp.hulls), DT, S, 1, hull_ids=smp.extras.get("hull_ids"),
+                              joints=smp.extras.get("joints"), body_body=workload != "c2")
+    bs = c["body_substeps"]
+    per_phase = {p: sum(v.values()) / bs for p, v in c["flops"].items()}
+    kinds = {k: sum(v[k] for v in c["flops"].values()) / bs for k in ("add", "mul", "div", "sqrt")}
+    return {"per_body_substep": c["total"] / bs, "per_phase": per_phase, "by_kind": kinds,
+            "sample": f"{n_worlds} worlds x {B} bodies x 1 frame x {S} substeps after {cfg['preroll']} pre-roll frames, oracle with counting scalar"}
+
+
+def parity_sample(workload, cfg, first_world, world_ids, frames, gpu38):
+    """Max position / orientation error of sampled worlds against the fp32 oracle stepped `frames` frames from the same
+    scene (row E: per-GPU summary statistics).  gpu38: (len(world_ids) * B, 38) f64 array downloaded from the device."""
+    import oracle_world as xw
+    B, S = cfg["bodies"], cfg["substeps"]
+    parts, ids, joints = [], [], []
+    hulls = None
+    for w in world_ids:
+        init, hulls, extras = xs.make_scene(workload, 1, first_world + int(w))
+        parts.append(init.reshape(-1, 38))
+        if "hull_ids" in extras:
+            ids.append(extras["hull_ids"]); joints.append(extras["joints"])
+    r = np.ascontiguousarray(np.concatenate(parts)).astype(np.float32)
+    if workload == "c2":
+        xo.step_bodies(r, hulls[0].vertices, DT, S, frames, threads=xo.hardware_threads())
+    else:
+        xw.step_worlds(r, B, list(hulls), DT, S, frames, threads=xo.hardware_threads(),
+                       hull_ids=np.concatenate(ids) if ids else None, joints=np.concatenate(joints) if joints else None)
+    c = r.astype(np.float64)
+    g = np.asarray(gpu38, dtype=np.float64).reshape(-1, 38)
+    pos = float(np.abs(g[:, 31:34] - c[:, 31:34]).max())
+    a, b = g[:, 34:38], c[:, 34:38]
+    av, as_, bv, bs = a[:, :3], a[:, 3], -b[:, :3], b[:, 3]
+    v = as_[:, None] * bv + bs[:, None] * av + np.cross(av, bv)
+    rot = float((2.0 * np.arcsin(np.clip(np.linalg.norm(v, axis=1), 0.0, 1.0))).max())
+    return pos, rot, bool(np.array_equal(g, c))

@@ -48,6 +48,33 @@ def step_worlds(rigids38, B, hulls, dt, substeps, frames, threads=1, hull_ids=No
     return {"constraints": int(ctr[0]), "pairs_tested": int(ctr[1]), "manifolds": int(ctr[2])}
 
 
+PHASES = ("integrate", "ground", "broadphase", "face_queries", "edge_query", "manifold", "sweep", "derive", "velocity")
+_L.xo_count_flops_worlds_f32.restype = C.c_uint64
+_L.xo_count_flops_worlds_f32.argtypes = [_VP, C.c_int64, C.c_int, _VP, C.c_int, _VP, _VP, C.c_int, C.c_double, C.c_double,
+                                         C.c_int, C.c_float, C.c_int, C.c_int, _VP]
+
+
+def count_flops_worlds(rigids38_f32, B, hulls, dt, substeps, frames, hull_ids=None, joints=None, compliance=1e-6, friction=1.0,
+                       body_body=True):
+    """Algorithmic flops of the specification (oracle instantiated with the counting scalar, oracle/xo_count.hpp): steps a
+    COPY of the given fp32 worlds for `frames` frames and returns {"constraints", "body_substeps", "flops": {phase: {add,
+    mul, div, sqrt}}, "total"} with add = mul = div = sqrt = 1 flop."""
+    r = np.ascontiguousarray(rigids38_f32, dtype=np.float32)
+    n_worlds = r.size // (38 * B)
+    harr, _keep = _hull_array(hulls)
+    ids = None if hull_ids is None else np.ascontiguousarray(hull_ids, dtype=np.int32)
+    J, jp = 0, None
+    if joints is not None:
+        joints = np.ascontiguousarray(joints, dtype=xo.JOINT_DTYPE).reshape(n_worlds, -1)
+        J, jp = joints.shape[1], C.c_void_p(joints.ctypes.data)
+    out = np.zeros((len(PHASES), 4), dtype=np.uint64)
+    cons = _L.xo_count_flops_worlds_f32(C.c_void_p(r.ctypes.data), n_worlds, B, C.cast(harr, _VP), len(hulls),
+                                        None if ids is None else C.c_void_p(ids.ctypes.data), jp, J, compliance, friction,
+                                        1 if body_body else 0, np.float32(dt), substeps, frames, C.c_void_p(out.ctypes.data))
+    flops = {p: dict(zip(("add", "mul", "div", "sqrt"), map(int, out[k]))) for k, p in enumerate(PHASES)}
+    return {"constraints": int(cons), "body_substeps": n_worlds * B * substeps * frames, "flops": flops, "total": int(out.sum())}
+
+
 def sat_manifold(fa7, fb7, hull_a, hull_b, dtype=np.float32):
     fa = np.ascontiguousarray(fa7, dtype=dtype); fb = np.ascontiguousarray(fb7, dtype=dtype)
     pts = np.zeros((4, 3), dtype=dtype); tg = np.zeros((4, 3), dtype=dtype)

@@ -41,7 +41,7 @@ def _staged_case(name, init, hulls, frames, sample, hull_ids=None, joints=None, 
                 os.environ.pop("XPBD_WORLD_PATH", None)
             else:
                 os.environ["XPBD_WORLD_PATH"] = old
-    assert st["kernel_launches"] >= 3 * 20 * frames, "the staged pipeline did not run"
+    assert st["kernel_launches"] >= 4 * 20 * frames, "the staged pipeline did not run"
     assert st["overflow_worlds"] == 0 and st["nan_worlds"] == 0
     assert np.array_equal(got, cpu.astype(np.float64)), f"{name}: GPU state differs from the fp32 oracle"
     print(f"smoke ok ({name}, staged pipeline): {n} worlds x {frames} frames, {st['constraints']} constraints, "

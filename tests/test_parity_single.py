@@ -166,6 +166,19 @@ def test_nan_world_does_not_poison_neighbours():
     assert np.isnan(g[5, 31:38]).any()
 
 
+def test_step_host_rigid_single_body_path():
+    """xpbd_batch_step_host_rigid on the reference's live path (one body per world): f64 records in and out."""
+    n = 300
+    init = scenes.c2_perturbed(n)
+    cpu, _ = _oracle(init, 12)
+    with cs.Worlds(n) as w:
+        w.add_hull(CUBE)
+        rec = init.copy()
+        for _ in range(12):
+            rec = w.integrate_host_rigid(rec, DT, 25, 1)
+    assert np.array_equal(xo.rigid38(rec), cpu.astype(np.float64))  # World::new's cube: all constants are fp32-exact
+
+
 def test_dynamic_snapshot_roundtrip_and_rewind():
     """The reference's rewind buffer (src/app.rs:48,204-215): snapshot, step, restore, step again -> same state."""
     n = 256
