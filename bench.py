@@ -222,6 +222,15 @@ class Bench:
         if cfg["preroll"]:
             self.w.integrate(DT, self.S, cfg["preroll"])  # untimed: bring the scene into contact
             self.frames_done += cfg["preroll"]
+        # every timed leg (value, e2e, e2e_rigid_f64) starts from this state and steps warmup + K frames: the legs evolve
+        # the same scene over the same frames, so their numbers are comparable
+        self.start_state = self.w.download_dynamic()
+        self.start_frames = self.frames_done
+
+    def rewind(self):
+        self.w.upload_dynamic(self.start_state)
+        self.w.sync()
+        self.frames_done = self.start_frames
 
     def barrier(self):
         if self.world_size > 1:
@@ -282,13 +291,14 @@ class Bench:
         self.w.set_sub_batches(0)
         return (acc / reps).tolist(), cand
 
-    def e2e_f32(self, steps):
+    def e2e_f32(self, steps, warmup):
         """Per step: H2D of every body's packed fp32 dynamic state from pinned memory, one frame, D2H of the result, sync."""
         torch, w = self.torch, self.w
+        self.rewind()
         pin_in = torch.empty((self.n_bodies, 13), dtype=torch.float32, pin_memory=True)
         pin_out = torch.empty((self.n_bodies, 13), dtype=torch.float32, pin_memory=True)
         w.download_dynamic_ptr(pin_in.data_ptr(), 0, self.n_worlds)
-        for _ in range(2):
+        for _ in range(warmup):
             w.integrate_host_ptr(DT, self.S, 1, pin_in.data_ptr(), pin_out.data_ptr(), sync=True)
             pin_in, pin_out = pin_out, pin_in
         self.barrier()
@@ -298,22 +308,23 @@ class Bench:
             pin_in, pin_out = pin_out, pin_in  # the state evolves exactly as in the device-resident run
         self.barrier()
         sec = self.max_over_ranks(time.perf_counter() - t0)
-        self.frames_done += 2 + steps
+        self.frames_done += warmup + steps
         io = self.n_bodies * 13 * 4
         return {"value": self.world_size * self.n_bodies * self.S * steps / sec, "unit": UNIT, "h2d_bytes_per_step": io,
                 "d2h_bytes_per_step": io,
                 "what": "xpbd_batch_step_host_f32 (pinned host buffers: H2D of every body's dynamic state, one frame, D2H of the result) + xpbd_batch_sync per step, wall clock"}
 
-    def e2e_rigid_f64(self, steps):
+    def e2e_rigid_f64(self, steps, warmup):
         """Per step: H2D of every body's full f64 record (the reference's `Rigid`, 304 B) from pinned memory, one frame,
         D2H of the records (13 dynamic values refreshed, f64 constants untouched), sync."""
         torch, w = self.torch, self.w
         from constraint_solver_b200 import _abi
+        self.rewind()
         nbytes = self.n_bodies * _abi.RIGID_DTYPE.itemsize
         pin = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
         rec = pin.numpy().view(_abi.RIGID_DTYPE)
         rec[:] = w.download().reshape(-1)
-        for _ in range(2):
+        for _ in range(warmup):
             w.integrate_host_rigid_ptr(DT, self.S, 1, pin.data_ptr(), pin.data_ptr(), sync=True)
         self.barrier()
         t0 = time.perf_counter()
@@ -321,7 +332,7 @@ class Bench:
             w.integrate_host_rigid_ptr(DT, self.S, 1, pin.data_ptr(), pin.data_ptr(), sync=True)  # in place, like `World` values
         self.barrier()
         sec = self.max_over_ranks(time.perf_counter() - t0)
-        self.frames_done += 2 + steps
+        self.frames_done += warmup + steps
         return {"value": self.world_size * self.n_bodies * self.S * steps / sec, "unit": UNIT, "h2d_bytes_per_step": nbytes,
                 "d2h_bytes_per_step": nbytes,
                 "what": "xpbd_batch_step_host_rigid (the reference's own 304-byte f64 Rigid records in pinned host memory: H2D of all 38 fields, one frame, D2H of the records) + xpbd_batch_sync per step, wall clock"}
@@ -440,8 +451,8 @@ def main():
     stats = dev["stats"]
     par = None if args.no_extras else b.parity()
     stage_ms, cand_pairs = b.stage_times()
-    e2e = b.e2e_f32(args.steps)
-    e2e64 = None if args.no_extras else b.e2e_rigid_f64(max(3, min(args.steps, 30)))
+    e2e = b.e2e_f32(args.steps, args.warmup)
+    e2e64 = None if args.no_extras else b.e2e_rigid_f64(args.steps, args.warmup)
 
     # ---- per-rank summary statistics, gathered once after the timed regions ----
     mine = [dev["rank_ms"], float(b.n_bodies * b.S * args.steps), float(stats["constraints"]), float(stats["overflow_worlds"]),
@@ -492,7 +503,7 @@ def main():
                 ob = Bench(wl, ocfg, 0, local_rank, 1, torch, dist)
                 k = max(3, min(args.steps, 30))
                 od = ob.device_resident(k, 3)
-                oe = ob.e2e_f32(k)
+                oe = ob.e2e_f32(k, 3)
                 ost = od["stats"]
                 others[wl] = {"value": od["value"], "unit": UNIT, "ms_per_step": od["ms_per_step"], "steps": k, "warmup": 3,
                               "config": workload_config(ocfg, 1, sub_batches=int(ost.get("sub_batches", 1))),

@@ -391,6 +391,7 @@ static int step_common(xpbd_batch* b, double dt, int32_t substep_count, int32_t 
     XPBD_CUDA_TRY(cudaEventRecord(b->ev_start, b->stream));
     XPBD_CUDA_TRY(cudaMemsetAsync(b->d_counters, 0, kBatchCounters * sizeof(unsigned long long), b->stream));
     b->stage_timed = false;
+    b->stage_ms_valid = false;
     b->last.sub_batches = 1;
     const bool world_path = b->desc.body_body_contacts != 0 || b->desc.joints_per_world > 0;
     // Host buffers: the staged pipeline consumes them per world range (copies on the range's stream) and clears the
@@ -457,7 +458,7 @@ int xpbd_batch_last_stats(xpbd_batch* b, xpbd_step_stats* out) {
     b->last.nan_worlds = (int32_t)std::min<unsigned long long>(b->h_counters[4], 0x7fffffffull);
     for (int k = 0; k < 4; ++k) {
         b->last.stage_ms[k] = 0.f;
-        if (b->stage_timed) XPBD_CUDA_TRY(cudaEventElapsedTime(&b->last.stage_ms[k], b->ev_stage[k], b->ev_stage[k + 1]));
+        if (b->stage_timed && b->stage_ms_valid) XPBD_CUDA_TRY(cudaEventElapsedTime(&b->last.stage_ms[k], b->ev_stage[k], b->ev_stage[k + 1]));
     }
     if (cnt[2]) set_error("TMA hull staging fell back to plain loads in %llu blocks", cnt[2]);
     *out = b->last;

@@ -106,6 +106,7 @@ struct xpbd_batch {
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     cudaEvent_t ev_stage[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // staged pipeline: around the last substep's kernels
     bool stage_timed = false;
+    bool stage_ms_valid = false;   // ev_stage[] were recorded by the last step call (not when the chains ran as CUDA graphs)
     xpbd_step_stats last{};
     bool stepped = false;
     void* world_scratch = nullptr;  // owned by the multi-body path

@@ -731,8 +731,22 @@ __global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------
+constexpr int kGraphMaxSubsteps = 256;  // longer chains (many frames per call) launch directly
+struct RangeGraphKey {    // everything the captured chain of one world range depends on (compared bytewise: zero-filled first)
+    StagedParams params;  // of the range, cand_stat = nullptr
+    int total;            // substeps in the chain
+    int grid[4];
+    const void* fn[3];    // prepare, sat, manifold kernels
+};
+struct RangeGraph {
+    cudaGraphExec_t exec = nullptr;
+    RangeGraphKey key;
+    void release() { if (exec) cudaGraphExecDestroy(exec); exec = nullptr; }
+};
+
 struct StagedState {
     StagedBuffers buf;
+    RangeGraph graphs[8];
     int64_t n_worlds = 0;
     size_t n_hulls = 0;  // kernel choices depend on the registered hulls
     int B = 0;
@@ -771,6 +785,7 @@ constexpr int kWorkCountStride = 32;  // uint32 words between the work counters 
 constexpr int kMaxSubBatches = 8;
 
 static void destroy_staged(StagedState* st) {
+    for (RangeGraph& g : st->graphs) g.release();
     st->buf.release();
     st->release_streams();
     if (st->d_range_counters) cudaFree(st->d_range_counters);
@@ -960,6 +975,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
     StagedState* st = nullptr;
     if (int rc = ensure_staged(b, st)) return rc;
     StagedParams P;
+    std::memset(&P, 0, sizeof P);  // (padding included: the ranges' graph keys compare these bytes)
     P.bodies = b->arrays;
     P.n_worlds = b->desc.n_worlds;
     P.B = B;
@@ -993,7 +1009,20 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
     const bool fork = n_sub > 1 && b->fork_needed;
     if (fork) XPBD_CUDA_TRY(cudaEventRecord(st->ev_fork, b->stream));
     const int64_t worlds_per_block = (int64_t)st->warps_prepare * (32 / st->prepare_lanes);
-    for (int k = 0; k < n_sub; ++k) {
+    // CUDA Graph per world range: with several ranges in flight, the chain of `total` substeps x 4 kernels of a range is
+    // captured once per (range, step parameters) and replayed with one cudaGraphLaunch per step call instead of
+    // 4 x total launches (C3: 320 launches per frame -> 4 graph launches).  The chain is the same sequence of kernels with
+    // the same arguments, so results cannot change.  Single-range calls launch directly: they are the ones whose stages
+    // are timed with events between the kernels (xpbd_step_stats.stage_ms).  XPBD_GRAPH=0 switches the graphs off.
+    bool use_graph = n_sub > 1 && total <= kGraphMaxSubsteps;
+    if (const char* e = std::getenv("XPBD_GRAPH")) use_graph = use_graph && e[0] != '0';
+    int ranges_started = 0;  // ranges whose stream has work of this call: they must be joined even when a later range fails
+    auto join_started = [&]() {
+        for (int k = 0; k < ranges_started && n_sub > 1; ++k) {
+            if (cudaEventRecord(st->sub_done[k], st->sub_streams[k]) == cudaSuccess) cudaStreamWaitEvent(b->stream, st->sub_done[k], 0);
+        }
+    };
+    auto run_range = [&](int k) -> int {
         // contiguous world range [w0, w0 + nw) of this sub-batch: every per-world / per-body pointer is advanced to it,
         // so the kernels see an ordinary batch of nw worlds
         const int64_t w0 = P.n_worlds * k / n_sub, nw = P.n_worlds * (k + 1) / n_sub - w0;
@@ -1019,6 +1048,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
             stream = st->sub_streams[k];
             Q.counters = st->d_range_counters + 4 * k;
             if (fork) XPBD_CUDA_TRY(cudaStreamWaitEvent(stream, st->ev_fork, 0));
+            ranges_started = k + 1;
             XPBD_CUDA_TRY(cudaMemsetAsync(Q.counters, 0, 4 * sizeof(unsigned long long), stream));
             if (int rc = rigid_io_before(b, g0, nw * B, stream)) return rc;  // xpbd_batch_step_host_rigid, same per-range pipelining
             if (b->io_in) {  // xpbd_batch_step_host_f32: this range's state from the host, under the other ranges' kernels
@@ -1026,37 +1056,83 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
                 launch_dyn_unpack(b->d_dyn_stage + 13 * g0, b->arrays, g0, nw * B, stream);
             }
         }
-        XPBD_CUDA_TRY(cudaMemsetAsync(S.overflow, 0, (size_t)nw * sizeof(int), stream));
         const int grid_prepare = (int)std::min<int64_t>((nw + worlds_per_block - 1) / worlds_per_block, (int64_t)st->n_sm * st->occ_prepare);
         const int grid_sat = (int)std::min<int64_t>((nw * S.capP + st->sat_cands_per_block - 1) / st->sat_cands_per_block, (int64_t)st->n_sm * occ_sat);
         const int grid_manifold = (int)std::min<int64_t>((nw * S.capP + 127) / 128, (int64_t)st->n_sm * st->occ_manifold);
         unsigned grid_solve = (unsigned)((2 * nw + 127) / 128);
         if (st->solve_blocks_per_sm > 0) grid_solve = std::min(grid_solve, (unsigned)(st->solve_blocks_per_sm * st->n_sm));
-        for (int s = 0; s < total; ++s) {
-            const bool last = s == total - 1;
-            const bool timed = last && k == 0;  // per-stage device times of the last substep (xpbd_step_stats.stage_ms): range 0
-            Q.cand_stat = last ? Q.counters + 3 : nullptr;
-            if (timed) cudaEventRecord(b->ev_stage[0], stream);
-            st->prepare_fn<<<grid_prepare, 32 * st->warps_prepare, st->smem_prepare, stream>>>(Q);
-            if (timed) cudaEventRecord(b->ev_stage[1], stream);
-            if (P.body_body) st->sat_fn<<<grid_sat, st->sat_threads, st->smem_sat, stream>>>(Q);
-            if (timed) cudaEventRecord(b->ev_stage[2], stream);
-            if (P.body_body) st->manifold_fn<<<grid_manifold, kManifoldThreads, st->smem_manifold, stream>>>(Q);
-            if (timed) cudaEventRecord(b->ev_stage[3], stream);
-            stage_solve_kernel<<<grid_solve, 128, 0, stream>>>(Q);
-            if (timed) cudaEventRecord(b->ev_stage[4], stream);
+        // the chain of this range: overflow flags reset, then `total` substeps of (prepare, sat, manifold, solve)
+        auto enqueue_chain = [&](bool with_events) -> int {
+            XPBD_CUDA_TRY(cudaMemsetAsync(S.overflow, 0, (size_t)nw * sizeof(int), stream));
+            for (int s = 0; s < total; ++s) {
+                const bool last = s == total - 1;
+                const bool timed = with_events && last && k == 0;  // per-stage device times of the last substep (xpbd_step_stats.stage_ms): range 0
+                Q.cand_stat = last ? Q.counters + 3 : nullptr;
+                if (timed) cudaEventRecord(b->ev_stage[0], stream);
+                st->prepare_fn<<<grid_prepare, 32 * st->warps_prepare, st->smem_prepare, stream>>>(Q);
+                if (timed) cudaEventRecord(b->ev_stage[1], stream);
+                if (P.body_body) st->sat_fn<<<grid_sat, st->sat_threads, st->smem_sat, stream>>>(Q);
+                if (timed) cudaEventRecord(b->ev_stage[2], stream);
+                if (P.body_body) st->manifold_fn<<<grid_manifold, kManifoldThreads, st->smem_manifold, stream>>>(Q);
+                if (timed) cudaEventRecord(b->ev_stage[3], stream);
+                stage_solve_kernel<<<grid_solve, 128, 0, stream>>>(Q);
+                if (timed) cudaEventRecord(b->ev_stage[4], stream);
+            }
+            XPBD_CUDA_TRY(cudaGetLastError());
+            return XPBD_OK;
+        };
+        if (use_graph) {
+            RangeGraph& G = st->graphs[k];
+            RangeGraphKey key;
+            std::memset(&key, 0, sizeof key);
+            key.params = Q; key.params.cand_stat = nullptr;
+            key.total = total; key.grid[0] = grid_prepare; key.grid[1] = grid_sat; key.grid[2] = grid_manifold; key.grid[3] = (int)grid_solve;
+            key.fn[0] = (const void*)st->prepare_fn; key.fn[1] = (const void*)st->sat_fn; key.fn[2] = (const void*)st->manifold_fn;
+            if (!G.exec || std::memcmp(&G.key, &key, sizeof key) != 0) {
+                G.release();
+                cudaGraph_t graph = nullptr;
+                XPBD_CUDA_TRY(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+                const int rc = enqueue_chain(false);
+                const cudaError_t ce = cudaStreamEndCapture(stream, &graph);
+                if (rc != XPBD_OK || ce != cudaSuccess) {
+                    if (graph) cudaGraphDestroy(graph);
+                    return rc != XPBD_OK ? rc : fail(XPBD_ERR_CUDA, "cudaStreamEndCapture failed: %s", cudaGetErrorString(ce));
+                }
+                const cudaError_t ie = cudaGraphInstantiate(&G.exec, graph, 0);
+                cudaGraphDestroy(graph);
+                if (ie != cudaSuccess) { G.exec = nullptr; return fail(XPBD_ERR_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(ie)); }
+                std::memcpy(&G.key, &key, sizeof key);
+            }
+            XPBD_CUDA_TRY(cudaGraphLaunch(G.exec, stream));
+        } else {
+            if (int rc = enqueue_chain(true)) return rc;
         }
         if (n_sub > 1 && b->io_out) {  // ... and its result back to the host
             launch_dyn_pack(b->arrays, b->d_dyn_stage + 13 * g0, g0, nw * B, stream);
             XPBD_CUDA_TRY(cudaMemcpyAsync(b->io_out + 13 * g0, b->d_dyn_stage + 13 * g0, (size_t)(nw * B) * 13 * sizeof(float), cudaMemcpyDeviceToHost, stream));
         }
         if (n_sub > 1) { if (int rc = rigid_io_after(b, g0, nw * B, stream)) return rc; }
-        if (n_sub > 1) {
+        if (n_sub > 1)
             XPBD_CUDA_TRY(cudaMemcpyAsync(st->h_range_counters + 4 * k, Q.counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
-            XPBD_CUDA_TRY(cudaEventRecord(st->sub_done[k], stream));
-            XPBD_CUDA_TRY(cudaStreamWaitEvent(b->stream, st->sub_done[k], 0));  // join: the batch stream sees the step call as one operation
+        return XPBD_OK;
+    };
+    for (int k = 0; k < n_sub; ++k) {
+        if (int rc = run_range(k)) {
+            // a failure in the middle: the ranges already forked are joined into the batch stream (the caller's stream sees
+            // everything that was enqueued), and the next step call forks again
+            join_started();
+            b->fork_needed = true;
+            b->io_in = nullptr; b->io_out = nullptr; b->io_rigid_in = nullptr; b->io_rigid_out = nullptr;
+            return rc;
         }
     }
+    if (n_sub > 1) {
+        for (int k = 0; k < n_sub; ++k) {  // join: the batch stream sees the step call as one operation
+            XPBD_CUDA_TRY(cudaEventRecord(st->sub_done[k], st->sub_streams[k]));
+            XPBD_CUDA_TRY(cudaStreamWaitEvent(b->stream, st->sub_done[k], 0));
+        }
+    }
+    b->stage_ms_valid = !use_graph;
     b->fork_needed = false;
     if (n_sub > 1) { b->io_in = nullptr; b->io_out = nullptr; b->io_rigid_in = nullptr; b->io_rigid_out = nullptr; }  // consumed per range
     b->last.sub_batches = n_sub;
