@@ -70,6 +70,34 @@ std::vector<uint32_t> pack_hull_blob(const std::vector<HostHull>& hulls) {
         int mfv = 0;
         for (int f = 0; f < d.n_faces; ++f) mfv = std::max(mfv, H.face_offsets[f + 1] - H.face_offsets[f]);
         d.max_face_verts = mfv;
+        // box classes: 3 groups of 4 edges whose fp32 object-space vectors are equal up to sign, bit for bit
+        if (d.n_verts == 8 && d.n_edges == 12) {
+            double ev[12][3];
+            for (int e = 0; e < 12; ++e)
+                for (int k = 0; k < 3; ++k)
+                    ev[e][k] = (double)(float)H.vertices[3 * H.edges[2 * e + 1] + k] - (double)(float)H.vertices[3 * H.edges[2 * e] + k];
+            int cls[12], n_cls = 0, count[12] = {0};
+            for (int e = 0; e < 12; ++e) {
+                cls[e] = -1;
+                for (int f = 0; f < e && cls[e] < 0; ++f) {
+                    const bool same = ev[e][0] == ev[f][0] && ev[e][1] == ev[f][1] && ev[e][2] == ev[f][2];
+                    const bool opposite = ev[e][0] == -ev[f][0] && ev[e][1] == -ev[f][1] && ev[e][2] == -ev[f][2];
+                    if (same || opposite) cls[e] = cls[f];
+                }
+                if (cls[e] < 0) cls[e] = n_cls++;
+                ++count[cls[e]];
+            }
+            const bool nonzero = [&] { for (int e = 0; e < 12; ++e) if (ev[e][0] == 0 && ev[e][1] == 0 && ev[e][2] == 0) return false; return true; }();
+            if (n_cls == 3 && count[0] == 4 && count[1] == 4 && count[2] == 4 && nonzero) {
+                unsigned long long perm = 0;
+                int k = 0;
+                for (int c = 0; c < 3; ++c)
+                    for (int e = 0; e < 12; ++e)
+                        if (cls[e] == c) perm |= (unsigned long long)e << (4 * k++);
+                d.edge_perm_lo = (uint32_t)perm; d.edge_perm_hi = (uint32_t)(perm >> 32);
+                d.box_classes = 1;
+            }
+        }
     }
     std::vector<uint32_t> blob(words, 0u);
     for (size_t h = 0; h < n; ++h) {

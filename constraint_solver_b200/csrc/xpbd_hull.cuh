@@ -25,7 +25,12 @@ struct HullDesc {
     float cx, cy, cz;   // centroid (object space)
     float radius;       // max |vertex - centroid| (bounding sphere for the broadphase)
     int32_t max_face_verts;
-    int32_t pad[3];
+    // Box-like hulls (8 vertices, 12 edges whose fp32 object-space edge vectors fall into 3 classes of 4 EXACTLY parallel
+    // edges — cubes and axis-scaled boxes): edge_perm = the 12 edge indices sorted by class, 4 bits each (entry k in bits
+    // [4k, 4k + 4) of lo | hi << 32); box_classes = 1.  Otherwise box_classes = 0.  Used by the thread-per-candidate SAT
+    // kernel to cull four parallel edges of B with one test.
+    uint32_t edge_perm_lo, edge_perm_hi;
+    int32_t box_classes;
 };
 static_assert(sizeof(HullDesc) == 64, "HullDesc must be 64 bytes");
 

@@ -136,9 +136,27 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
             const EdgeCull cull = make_edge_cull(da, db, __int_as_float((int)rkey), S.vert(8 + wi.x), S.vert(8 + wi.y));
             const float tm = fabsf(cull.T) + cull.M;
             const float K = tm * tm, Kf = cull.M * cull.M;
+            // B's 12 edge vectors in registers, sorted by parallel class when B is box-like (HullDesc::box_classes; entry k
+            // is hull edge perm[k], classes are k = 0-3, 4-7, 8-11), else in hull order
+            const bool boxB = hB.box_classes != 0;
+            const unsigned long long perm = boxB ? ((unsigned long long)hB.edge_perm_lo | ((unsigned long long)hB.edge_perm_hi << 32))
+                                                 : 0xBA9876543210ull;
             V3 eb[12];
 #pragma unroll
-            for (int jb = 0; jb < 12; ++jb) { const int2 e = EB[jb]; eb[jb] = S.vert(8 + e.y) - S.vert(8 + e.x); }
+            for (int k = 0; k < 12; ++k) { const int2 e = EB[(int)(perm >> (4 * k)) & 15]; eb[k] = S.vert(8 + e.y) - S.vert(8 + e.x); }
+            // Class-level cull (box-like B).  The world-space vectors of B's parallel edges are the same real vector up to
+            // the fp32 rounding of their end points: |b_p -+ b_rep| <= beta per component, with beta >= 4 eps_W + 2 ulp where
+            // eps_W <= 20 u rho + u R bounds the rounding of frame * vertex (u = 2^-24, rho = largest |object-space vertex|,
+            // R = largest |world coordinate|).  Hence c_p = edge_a x b_p differs from +-c_rep by at most e_c = 2 |a| beta
+            // (|a| in the 1-norm), and with N' = -us_rep - e_c max|d_i| - tm e_c and G' = |f_rep| - e_c |dC| - M e_c:
+            //     N' > tm |c_rep|,  G' > M |c_rep|,  |c_rep| > 2 e_c
+            // imply, for each of the four pairs, exactly the per-pair conditions below (us < 0, us^2 > K c2, f^2 > Kf c2,
+            // c2 > 1e-24) in real arithmetic — the flip sign of every pair equals the representative's (up to the pair's
+            // edge orientation, which cancels in s c).  One test then drops four pairs; a class that is not provably
+            // droppable (the contact's own classes, nearly parallel classes whose cross product is rounding noise,
+            // far-away coordinates) falls back to the per-pair tests, so nothing is decided differently — only sooner.
+            const float rhoB = fabsf(hB.cx) + fabsf(hB.cy) + fabsf(hB.cz) + hB.radius;
+            const float beta = 1e-5f * rhoB + 1e-6f * __int_as_float((int)rkey);
 #pragma unroll 1
             for (int ia = 0; ia < 12; ++ia) {
                 const int2 ea = EA[ia];
@@ -147,17 +165,37 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
                 // per edge of A: the three vectors every pair of this edge is tested against (the estimate c . (w - foot) is
                 // taken as one dot product with the difference: fewer operations and less cancellation than c.w - c.foot)
                 const V3 d1 = cull.w1 - foot, d2 = cull.w2 - foot, dC = foot - CA;
+                const float e_c = 2.0f * (fabsf(edge_a.x) + fabsf(edge_a.y) + fabsf(edge_a.z)) * beta;
+                const float dmax = fmaxf(fabsf(d1.x) + fabsf(d1.y) + fabsf(d1.z), fabsf(d2.x) + fabsf(d2.y) + fabsf(d2.z));
+                const float h1 = e_c * dmax + tm * e_c;
+                const float g0 = e_c * (fabsf(dC.x) + fabsf(dC.y) + fabsf(dC.z)) + cull.M * e_c;
+                const float c2min = 4.0f * e_c * e_c + 4e-24f;
                 uint32_t bits = 0;
 #pragma unroll
-                for (int jb = 0; jb < 12; ++jb) {
-                    const V3 c = cross(edge_a, eb[jb]);
-                    const float c2 = dot(c, c);
-                    const float f = dot(c, dC);
-                    const float u1 = dot(c, d1), u2 = dot(c, d2);
-                    const float us = f < 0.0f ? -fmaxf(u1, u2) : fminf(u1, u2);  // the smaller of the two bounds, flipped like the axis
-                    const bool below = us < 0.0f && fmul(us, us) > fmul(K, c2) && fmul(f, f) > fmul(Kf, c2) && c2 > 1e-24f;
-                    const bool keep = !below && c2 > 0.0f;
-                    bits |= (keep ? 1u : 0u) << jb;
+                for (int j = 0; j < 3; ++j) {
+                    bool class_culled = false;
+                    if (boxB) {
+                        const V3 c = cross(edge_a, eb[4 * j]);
+                        const float c2 = dot(c, c);
+                        const float f = dot(c, dC);
+                        const float u1 = dot(c, d1), u2 = dot(c, d2);
+                        const float us = f < 0.0f ? -fmaxf(u1, u2) : fminf(u1, u2);
+                        const float Np = -us - h1, Gp = fabsf(f) - g0;
+                        class_culled = Np > 0.0f && Np * Np > K * c2 && Gp > 0.0f && Gp * Gp > Kf * c2 && c2 > c2min;
+                    }
+                    if (!class_culled) {
+#pragma unroll
+                        for (int k = 4 * j; k < 4 * j + 4; ++k) {
+                            const V3 c = cross(edge_a, eb[k]);
+                            const float c2 = dot(c, c);
+                            const float f = dot(c, dC);
+                            const float u1 = dot(c, d1), u2 = dot(c, d2);
+                            const float us = f < 0.0f ? -fmaxf(u1, u2) : fminf(u1, u2);  // the smaller of the two bounds, flipped like the axis
+                            const bool below = us < 0.0f && fmul(us, us) > fmul(K, c2) && fmul(f, f) > fmul(Kf, c2) && c2 > 1e-24f;
+                            const bool keep = !below && c2 > 0.0f;
+                            bits |= (keep ? 1u : 0u) << ((int)(perm >> (4 * k)) & 15);
+                        }
+                    }
                 }
                 *S.mask(ia) = bits;
             }

@@ -93,7 +93,7 @@ pub struct xpbd_step_stats {
     pub stage_ms: [f32; 4],
     pub candidate_pairs: u64,
     pub sub_batches: i32,
-    pub reserved: i32,
+    pub nan_worlds: i32,
 }
 
 #[repr(C)]
@@ -101,11 +101,19 @@ pub struct xpbd_batch {
     _private: [u8; 0],
 }
 
+pub const XPBD_MAX_MANIFOLD: usize = 4;
+
+// Every entry point of include/xpbd_b200.h, in the header's order (tests/test_abi.py diffs names and argument counts).
 extern "C" {
     pub fn xpbd_last_error() -> *const c_char;
+    pub fn xpbd_version() -> *const c_char;
     pub fn xpbd_device_count(count: *mut i32) -> c_int;
     pub fn xpbd_polytope_rigid_metrics(hull: *const xpbd_polytope, density: f64, out: *mut xpbd_rigid_metrics) -> c_int;
     pub fn xpbd_rigid_new(metrics: *const xpbd_rigid_metrics, out: *mut xpbd_rigid) -> c_int;
+    pub fn xpbd_polytope_planes(hull: *const xpbd_polytope, out: *mut f64) -> c_int;
+    pub fn xpbd_quickhull(points: *const f64, n_points: i32, vertices: *mut f64, n_vertices: *mut i32, edges: *mut i32,
+                          n_edges: *mut i32, face_offsets: *mut i32, face_indices: *mut i32, n_faces: *mut i32,
+                          n_face_indices: *mut i32, centroid: *mut f64) -> c_int;
     pub fn xpbd_batch_create(desc: *const xpbd_batch_desc, out: *mut *mut xpbd_batch) -> c_int;
     pub fn xpbd_batch_destroy(batch: *mut xpbd_batch) -> c_int;
     pub fn xpbd_batch_add_hull(batch: *mut xpbd_batch, hull: *const xpbd_polytope, hull_id: *mut i32) -> c_int;
@@ -114,6 +122,7 @@ extern "C" {
     pub fn xpbd_batch_set_stream(batch: *mut xpbd_batch, cuda_stream: *mut c_void) -> c_int;
     pub fn xpbd_batch_set_sub_batches(batch: *mut xpbd_batch, count: i32) -> c_int;
     pub fn xpbd_batch_step_host_f32(batch: *mut xpbd_batch, dt: f64, substep_count: i32, n_frames: i32, input: *const f32, output: *mut f32) -> c_int;
+    pub fn xpbd_batch_step_host_rigid(batch: *mut xpbd_batch, dt: f64, substep_count: i32, n_frames: i32, input: *const xpbd_rigid, output: *mut xpbd_rigid) -> c_int;
     pub fn xpbd_batch_upload(batch: *mut xpbd_batch, first: i64, n: i64, rigids: *const xpbd_rigid) -> c_int;
     pub fn xpbd_batch_download(batch: *mut xpbd_batch, first: i64, n: i64, rigids: *mut xpbd_rigid) -> c_int;
     pub fn xpbd_batch_upload_broadcast(batch: *mut xpbd_batch, world_bodies: *const xpbd_rigid) -> c_int;
@@ -132,6 +141,15 @@ extern "C" {
                              out: *mut xpbd_constraint, counts: *mut i32) -> c_int;
     pub fn xpbd_solve_batch(rigids: *mut xpbd_rigid, n: i64, constraints: *const xpbd_constraint, counts: *const i32,
                             stride: i32, dt: f64, compliance: f64) -> c_int;
+    pub fn xpbd_face_axes_separation_batch(frames_a: *const xpbd_frame, frames_b: *const xpbd_frame, n: i64, hull_a: *const xpbd_polytope,
+                                           hull_b: *const xpbd_polytope, distance: *mut f64, face: *mut i32) -> c_int;
+    pub fn xpbd_edge_axes_separation_batch(frames_a: *const xpbd_frame, frames_b: *const xpbd_frame, n: i64, hull_a: *const xpbd_polytope,
+                                           hull_b: *const xpbd_polytope, distance: *mut f64, edges: *mut i32) -> c_int;
+    pub fn xpbd_sat_manifold_batch(frames_a: *const xpbd_frame, frames_b: *const xpbd_frame, n: i64, hull_a: *const xpbd_polytope,
+                                   hull_b: *const xpbd_polytope, out: *mut xpbd_constraint, counts: *mut i32, feature: *mut i32) -> c_int;
+    pub fn xpbd_sat_feature_batch(frames_a: *const xpbd_frame, frames_b: *const xpbd_frame, n: i64, hull_a: *const xpbd_polytope,
+                                  hull_b: *const xpbd_polytope, schedule: i32, cull: i32, feature: *mut i32, index: *mut i32) -> c_int;
+    pub fn xpbd_fp32_peak_microbench(device: i32, use_fma: i32, tflops: *mut f64) -> c_int;
 }
 
 /// Panics with the library's error text: the reference's own failure mode is a panic (src/rigid.rs:59).

@@ -81,6 +81,51 @@ impl Worlds {
         }
     }
 
+    /// Hull id of every body of worlds [first_world, ...): `ids.len()` = n_worlds x bodies_per_world (mixed-hull scenes, C4).
+    pub fn set_hulls(&mut self, first_world: usize, ids: &[i32]) {
+        let n = ids.len() / self.bodies_per_world;
+        ffi::check(unsafe { ffi::xpbd_batch_set_hulls(self.handle, first_world as i64, n as i64, ids.as_ptr()) });
+    }
+
+    /// Distance / attachment joints (`Constraint.distance`, src/constraint.rs:9) of worlds [first_world, ...):
+    /// `joints.len()` = n_worlds x joints_per_world; `body_a < 0` marks an unused slot, `body_b < 0` a world-space anchor.
+    pub fn set_joints(&mut self, first_world: usize, joints: &[ffi::xpbd_joint], joints_per_world: usize) {
+        let n = joints.len() / joints_per_world;
+        ffi::check(unsafe { ffi::xpbd_batch_set_joints(self.handle, first_world as i64, n as i64, joints.as_ptr()) });
+    }
+
+    /// World ranges the multi-body pipeline steps concurrently (0 = automatic); results do not depend on it.
+    pub fn set_sub_batches(&mut self, count: i32) {
+        ffi::check(unsafe { ffi::xpbd_batch_set_sub_batches(self.handle, count) });
+    }
+
+    /// The rewind buffer of the app (`states: Vec<(World, DebugLines)>`, src/app.rs:48,146-148) without the 304-byte
+    /// records: 13 packed fp32 values per body (position, rotation, velocity, angular velocity).
+    pub fn download_dynamic(&mut self, first_world: usize, n_worlds: usize) -> Vec<f32> {
+        let mut out = vec![0f32; n_worlds * self.bodies_per_world * 13];
+        ffi::check(unsafe { ffi::xpbd_batch_download_dynamic_f32(self.handle, first_world as i64, n_worlds as i64, out.as_mut_ptr()) });
+        out
+    }
+
+    pub fn upload_dynamic(&mut self, first_world: usize, snapshot: &[f32]) {
+        let n = snapshot.len() / (self.bodies_per_world * 13);
+        ffi::check(unsafe { ffi::xpbd_batch_upload_dynamic_f32(self.handle, first_world as i64, n as i64, snapshot.as_ptr()) });
+    }
+
+    /// `World::integrate` for callers whose state lives in host memory as the reference's own records: uploads
+    /// `rigids` (all worlds), steps, and writes the new velocity / angular velocity / position / rotation back; every
+    /// other field keeps its f64 value (xpbd_batch_step_host_rigid; the copies are pipelined per world range).
+    pub fn integrate_host(&mut self, rigids: &mut [Rigid], dt: f64, substep_count: usize, n_frames: usize) {
+        assert_eq!(rigids.len(), self.n_worlds * self.bodies_per_world);
+        let mut recs: Vec<ffi::xpbd_rigid> = rigids.iter().map(|r| r.to_ffi()).collect();
+        let p = recs.as_mut_ptr();
+        ffi::check(unsafe { ffi::xpbd_batch_step_host_rigid(self.handle, dt, substep_count as i32, n_frames as i32, p, p) });
+        ffi::check(unsafe { ffi::xpbd_batch_sync(self.handle) });
+        for (r, rec) in rigids.iter_mut().zip(&recs) {
+            r.update_from_ffi(rec);
+        }
+    }
+
     /// `World::integrate` for every world: `n_frames` frames of `substep_count` substeps.
     pub fn integrate(&mut self, dt: f64, substep_count: usize, n_frames: usize) {
         ffi::check(unsafe { ffi::xpbd_batch_step(self.handle, dt, substep_count as i32, n_frames as i32) });

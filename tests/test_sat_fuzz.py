@@ -221,6 +221,20 @@ def test_scaled_boxes_every_schedule_and_cull_agree(sa, sb):
             _ab(fa, fb, ha, hb, CUBE_SCHEDULES, oracle_sample=200)
 
 
+def test_hexahedra_that_are_not_boxes_take_the_per_pair_cull():
+    """A frustum has 8 vertices, 12 edges and 6 quads — every all-cube schedule applies — but its slanted edges are not
+    parallel: the hull table must not classify it as box-like (HullDesc::box_classes), and the thread-per-candidate
+    kernel's class-level cull must fall back to the per-pair tests.  Frustum vs frustum and frustum vs cube."""
+    v = CUBE.vertices.copy()
+    top = v[:, 2] == 1.0
+    v[top, 0:2] = 0.5 + 0.6 * (v[top, 0:2] - 0.5)
+    frustum = cs.Polytope(v, CUBE.edges, CUBE.faces, (0.5, 0.5, 0.45))
+    rng = np.random.default_rng(23)
+    for ha, hb in ((frustum, frustum), (CUBE, frustum), (frustum, CUBE)):
+        for fa, fb in (regime_random(rng, N // 2, ha, hb, 1.0), regime_stack(rng, N // 2, ha, hb, 1.0)):
+            _ab(fa, fb, ha, hb, CUBE_SCHEDULES, oracle_sample=200)
+
+
 def test_general_hull_pairs_cull_agrees_with_full_scan():
     """Tetrahedron / icosahedron / QuickHull hulls: the warp-per-candidate kernel with and without the cull."""
     hulls = scenes.c4_hulls()
