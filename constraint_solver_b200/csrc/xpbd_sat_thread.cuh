@@ -144,19 +144,23 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
             V3 eb[12];
 #pragma unroll
             for (int k = 0; k < 12; ++k) { const int2 e = EB[(int)(perm >> (4 * k)) & 15]; eb[k] = S.vert(8 + e.y) - S.vert(8 + e.x); }
-            // Class-level cull (box-like B).  The world-space vectors of B's parallel edges are the same real vector up to
-            // the fp32 rounding of their end points: |b_p -+ b_rep| <= beta per component, with beta >= 4 eps_W + 2 ulp where
-            // eps_W <= 20 u rho + u R bounds the rounding of frame * vertex (u = 2^-24, rho = largest |object-space vertex|,
-            // R = largest |world coordinate|).  Hence c_p = edge_a x b_p differs from +-c_rep by at most e_c = 2 |a| beta
-            // (|a| in the 1-norm), and with N' = -us_rep - e_c max|d_i| - tm e_c and G' = |f_rep| - e_c |dC| - M e_c:
+            // Class-level cull (box-like B).  The world-space vectors of B's parallel edges are the same real vector up to the
+            // fp32 rounding of their end points.  With u = 2^-24, rho = largest |object-space vertex| of B and R = largest
+            // |world coordinate|, frame * vertex = (qv x (qv x v + v s)) 2 + v + p carries at most 49 u rho + u R of rounding
+            // per component (worst case, every operation's error aligned), so two parallel edge vectors differ by at most
+            // beta = 200 u rho + 4 u R per component (4 end points + the two subtractions), i.e. by sqrt(3) beta in length.
+            // Hence c_p = edge_a x b_p differs from +-c_rep by at most e_c = |a| (sqrt(3) beta + rounding of the two cross
+            // products), and with N' = -us_rep - e_c max|d_i| - tm e_c and G' = |f_rep| - e_c |dC| - M e_c the conditions
             //     N' > tm |c_rep|,  G' > M |c_rep|,  |c_rep| > 2 e_c
             // imply, for each of the four pairs, exactly the per-pair conditions below (us < 0, us^2 > K c2, f^2 > Kf c2,
             // c2 > 1e-24) in real arithmetic — the flip sign of every pair equals the representative's (up to the pair's
             // edge orientation, which cancels in s c).  One test then drops four pairs; a class that is not provably
             // droppable (the contact's own classes, nearly parallel classes whose cross product is rounding noise,
             // far-away coordinates) falls back to the per-pair tests, so nothing is decided differently — only sooner.
-            const float rhoB = fabsf(hB.cx) + fabsf(hB.cy) + fabsf(hB.cz) + hB.radius;
-            const float beta = 1e-5f * rhoB + 1e-6f * __int_as_float((int)rkey);
+            // (Lengths through sqrt.approx, rounded up by 1e-5.)
+            const float rhoB = 1.00001f * sqrt_approx(hB.cx * hB.cx + hB.cy * hB.cy + hB.cz * hB.cz) + hB.radius;
+            const float beta = 1.25e-5f * rhoB + 3e-7f * __int_as_float((int)rkey);  // 200 u = 1.19e-5, 4 u = 2.4e-7
+            const float e_unit = 1.7321f * beta + 8e-7f * hB.radius;                  // per unit length of edge_a
 #pragma unroll 1
             for (int ia = 0; ia < 12; ++ia) {
                 const int2 ea = EA[ia];
@@ -165,10 +169,10 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
                 // per edge of A: the three vectors every pair of this edge is tested against (the estimate c . (w - foot) is
                 // taken as one dot product with the difference: fewer operations and less cancellation than c.w - c.foot)
                 const V3 d1 = cull.w1 - foot, d2 = cull.w2 - foot, dC = foot - CA;
-                const float e_c = 2.0f * (fabsf(edge_a.x) + fabsf(edge_a.y) + fabsf(edge_a.z)) * beta;
-                const float dmax = fmaxf(fabsf(d1.x) + fabsf(d1.y) + fabsf(d1.z), fabsf(d2.x) + fabsf(d2.y) + fabsf(d2.z));
+                const float e_c = 1.00001f * sqrt_approx(edge_a.x * edge_a.x + edge_a.y * edge_a.y + edge_a.z * edge_a.z) * e_unit;
+                const float dmax = 1.00001f * sqrt_approx(fmaxf(d1.x * d1.x + d1.y * d1.y + d1.z * d1.z, d2.x * d2.x + d2.y * d2.y + d2.z * d2.z));
                 const float h1 = e_c * dmax + tm * e_c;
-                const float g0 = e_c * (fabsf(dC.x) + fabsf(dC.y) + fabsf(dC.z)) + cull.M * e_c;
+                const float g0 = e_c * 1.00001f * sqrt_approx(dC.x * dC.x + dC.y * dC.y + dC.z * dC.z) + cull.M * e_c;
                 const float c2min = 4.0f * e_c * e_c + 4e-24f;
                 uint32_t bits = 0;
 #pragma unroll
