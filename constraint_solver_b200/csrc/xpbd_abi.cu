@@ -62,8 +62,7 @@ std::vector<uint32_t> pack_hull_blob(const std::vector<HostHull>& hulls) {
         d.n_edges = (int32_t)(H.edges.size() / 2);
         d.vert_off = (int32_t)words;  words = align4(words + 4 * (size_t)d.n_verts);
         d.plane_off = (int32_t)words; words = align4(words + 4 * (size_t)d.n_faces);
-        // hulls with 8 vertices and 12 edges: 12 words of edge adjacency follow the edge list (see below)
-        d.edge_off = (int32_t)words;  words = align4(words + 2 * (size_t)d.n_edges + (d.n_verts == 8 && d.n_edges == 12 ? 12 : 0));
+        d.edge_off = (int32_t)words;  words = align4(words + 2 * (size_t)d.n_edges);
         d.foff_off = (int32_t)words;  words = align4(words + (size_t)d.n_faces + 1);
         d.fidx_off = (int32_t)words;  words = align4(words + H.face_indices.size());
         d.cx = (float)H.centroid[0]; d.cy = (float)H.centroid[1]; d.cz = (float)H.centroid[2];
@@ -113,23 +112,6 @@ std::vector<uint32_t> pack_hull_blob(const std::vector<HostHull>& hulls) {
             v[4 * i + 3] = 0.0f;
         }
         for (size_t e = 0; e < H.edges.size(); ++e) blob[d.edge_off + e] = (uint32_t)H.edges[e];
-        if (d.n_verts == 8 && d.n_edges == 12) {
-            // edge adjacency: for edge e = (x, y), the (up to two) other neighbours of x in bits 0-7 / 8-15 and of y in
-            // bits 16-23 / 24-31 (0xff = none) — the vertices the SAT cull tries as witnesses of the support test of A
-            for (int e = 0; e < 12; ++e) {
-                const int x = H.edges[2 * e], y = H.edges[2 * e + 1];
-                uint32_t w = 0xffffffffu;
-                int nx = 0, ny = 0;
-                for (int g = 0; g < 12; ++g) {
-                    if (g == e) continue;
-                    const int a = H.edges[2 * g], b = H.edges[2 * g + 1];
-                    const int ox = a == x ? b : (b == x ? a : -1), oy = a == y ? b : (b == y ? a : -1);
-                    if (ox >= 0 && ox != y && nx < 2) { w = (w & ~(0xffu << (8 * nx))) | ((uint32_t)ox << (8 * nx)); ++nx; }
-                    if (oy >= 0 && oy != x && ny < 2) { w = (w & ~(0xffu << (16 + 8 * ny))) | ((uint32_t)oy << (16 + 8 * ny)); ++ny; }
-                }
-                blob[d.edge_off + 24 + e] = w;
-            }
-        }
         for (size_t f = 0; f < H.face_offsets.size(); ++f) blob[d.foff_off + f] = (uint32_t)H.face_offsets[f];
         for (size_t k = 0; k < H.face_indices.size(); ++k) blob[d.fidx_off + k] = (uint32_t)H.face_indices[k];
     }

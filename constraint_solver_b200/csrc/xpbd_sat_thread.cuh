@@ -138,7 +138,6 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
             const float K = tm * tm, Kf = cull.M * cull.M;
             // B's 12 edge vectors in registers, sorted by parallel class when B is box-like (HullDesc::box_classes; entry k
             // is hull edge perm[k], classes are k = 0-3, 4-7, 8-11), else in hull order
-            const uint32_t* ENB = T.words + hA.edge_off + 24;  // A's edge adjacency (hull table, 8-vertex / 12-edge hulls)
             const bool boxB = hB.box_classes != 0;
             const unsigned long long perm = boxB ? ((unsigned long long)hB.edge_perm_lo | ((unsigned long long)hB.edge_perm_hi << 32))
                                                  : 0xBA9876543210ull;
@@ -197,21 +196,7 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
                             const float u1 = dot(c, d1), u2 = dot(c, d2);
                             const float us = f < 0.0f ? -fmaxf(u1, u2) : fminf(u1, u2);  // the smaller of the two bounds, flipped like the axis
                             const bool below = us < 0.0f && fmul(us, us) > fmul(K, c2) && fmul(f, f) > fmul(Kf, c2) && c2 > 1e-24f;
-                            bool keep = !below && c2 > 0.0f;
-                            if (keep && fmul(f, f) > fmul(Kf, c2) && c2 > 1e-24f) {
-                                // A-side witness: the reference skips a pair when some vertex of A lies further along the axis
-                                // than the edge foot (src/collision.rs:181-183).  If a neighbour v of the edge's end points
-                                // has s c . (v - foot) > M |c| — beyond every rounding of the reference's two dot products —
-                                // the pair is skipped there too, whatever its distance: drop it here.
-                                const uint32_t nb = ENB[ia];
-                                float g = -FLT_MAX;
-#pragma unroll
-                                for (int q = 0; q < 4; ++q) {
-                                    const int v = (nb >> (8 * q)) & 0xff;
-                                    if (v < 8) { const float t = dot(c, S.vert(v) - foot); g = fmaxf(g, f < 0.0f ? -t : t); }
-                                }
-                                if (g > 0.0f && fmul(g, g) > fmul(Kf, c2)) keep = false;
-                            }
+                            const bool keep = !below && c2 > 0.0f;
                             bits |= (keep ? 1u : 0u) << ((int)(perm >> (4 * k)) & 15);
                         }
                     }
