@@ -890,9 +890,8 @@ static int build_staged(xpbd_batch* b, StagedState* st) {
         const char* dual = std::getenv("XPBD_SAT_DUAL");
         const bool want_warp = (e && !std::strcmp(e, "warp")) || (dual && dual[0] == '0');
         const bool want_dual = e && !std::strcmp(e, "dual");
-        const bool thread_ok = H.bytes / 4 < 65536;  // the thread-per-candidate kernel packs two hull-table offsets into 32 bits
         if (all_cubes && !want_warp) {
-            if (want_dual || !thread_ok) {
+            if (want_dual) {
                 st->sat_fn = cull ? stage_sat_cubes_kernel<true> : stage_sat_cubes_kernel<false>;
                 st->sat_cands_per_block = 16;
             } else {
@@ -1230,7 +1229,6 @@ extern "C" int xpbd_sat_feature_batch(const xpbd_frame* fa, const xpbd_frame* fb
     void (*fn)(StagedParams) = nullptr;
     int threads = 256;
     size_t smem = dev.bytes + 8 * (size_t)sat_words_per_warp(maxV) * 4;
-    if (schedule == 2 && dev.bytes / 4 >= 65536) return fail(XPBD_ERR_CAPACITY, "hull table too large for schedule 2");
     if (schedule == 0) fn = cull ? stage_sat_kernel<true> : stage_sat_kernel<false>;
     else if (schedule == 1) fn = cull ? stage_sat_cubes_kernel<true> : stage_sat_cubes_kernel<false>;
     else { fn = cull ? stage_sat_thread_kernel<true> : stage_sat_thread_kernel<false>; threads = kSatThreadBlock; smem = sat_thread_smem_bytes(dev.bytes); }
