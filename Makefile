@@ -16,8 +16,12 @@ $(LIB): $(SRCS) $(HDRS)
 stats:
 	mkdir -p constraint_solver_b200/lib/debug
 	$(NVCC) $(NVCCFLAGS) -DXPBD_CULL_STATS -o constraint_solver_b200/lib/debug/libxpbd_b200_stats.so $(SRCS)
+# tuning variant: make variant NAME=sat5 EXTRA="-DXPBD_SAT_THREAD_MIN_BLOCKS=5" -> lib/variants/libxpbd_b200_sat5.so (XPBD_B200_LIB selects it)
+variant:
+	mkdir -p constraint_solver_b200/lib/variants
+	$(NVCC) $(NVCCFLAGS) $(EXTRA) -o constraint_solver_b200/lib/variants/libxpbd_b200_$(NAME).so $(SRCS)
 oracle:
 	$(MAKE) -C oracle
 clean:
 	rm -rf constraint_solver_b200/lib oracle/_build
-.PHONY: all lib oracle clean stats
+.PHONY: all lib oracle clean stats variant

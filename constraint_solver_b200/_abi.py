@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libxpbd_b200.so")
+# XPBD_B200_LIB: another build of the same library (tuning variants under lib/variants/, the -DXPBD_CULL_STATS debug build)
+LIB_PATH = os.environ.get("XPBD_B200_LIB") or os.path.join(_HERE, "lib", "libxpbd_b200.so")
 
 XPBD_OK = 0
 XPBD_ERR_INVALID = -1
