@@ -43,6 +43,15 @@ def main():
         for k in KEYS:
             if k in hdr:
                 print(f"  {k:95s} {r[hdr.index(k)]:>18s} {units[hdr.index(k)]}")
+        try:  # FP32 flops executed = (FADD + FMUL + 2 FFMA thread instructions per elapsed cycle) x elapsed cycles
+            g = lambda k: float(r[hdr.index(k)])
+            cyc = g("smsp__cycles_elapsed.max")
+            fl = (g("smsp__sass_thread_inst_executed_op_fadd_pred_on.sum.per_cycle_elapsed") +
+                  g("smsp__sass_thread_inst_executed_op_fmul_pred_on.sum.per_cycle_elapsed") +
+                  2 * g("smsp__sass_thread_inst_executed_op_ffma_pred_on.sum.per_cycle_elapsed")) * cyc
+            print(f"  {'derived: fp32 flops executed (fadd + fmul + 2 ffma)':95s} {fl:18.0f} flop  ({cyc:.0f} cycles elapsed)")
+        except (ValueError, KeyError):
+            pass
         print()
 
 
