@@ -177,7 +177,7 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
                 uint32_t bits = 0;
 #pragma unroll
                 for (int j = 0; j < 3; ++j) {
-                    bool class_culled = false, class_kept = false;
+                    bool class_culled = false;
                     if (boxB) {
                         const V3 c = cross(edge_a, eb[4 * j]);
                         const float c2 = dot(c, c);
@@ -186,17 +186,8 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
                         const float us = f < 0.0f ? -fmaxf(u1, u2) : fminf(u1, u2);
                         const float Np = -us - h1, Gp = fabsf(f) - g0;
                         class_culled = Np > 0.0f && Np * Np > K * c2 && Gp > 0.0f && Gp * Gp > Kf * c2 && c2 > c2min;
-                        // Not droppable although the representative is well conditioned (|c_rep| > 2 e_c): the four pairs see
-                        // the same axis up to e_c, so the per-pair tests would keep (nearly) all of them as well — keep the
-                        // whole class without running them.  Keeping a pair is always exact (it only goes through the
-                        // reference's arithmetic); the per-pair tests are worth their 4 x 46 instructions only where the cross
-                        // products are rounding noise and the four pairs really differ.
-                        class_kept = !class_culled && c2 > c2min;
                     }
-                    if (class_kept) {
-#pragma unroll
-                        for (int k = 4 * j; k < 4 * j + 4; ++k) bits |= 1u << ((int)(perm >> (4 * k)) & 15);
-                    } else if (!class_culled) {
+                    if (!class_culled) {
 #pragma unroll
                         for (int k = 4 * j; k < 4 * j + 4; ++k) {
                             const V3 c = cross(edge_a, eb[k]);
