@@ -589,15 +589,36 @@ XD void face_manifold(const HullTable& T, const HullDesc& hR, const HullDesc& hI
         if (cnt < kMaxClip) C.set(0, cnt++, ld3(WI, T.face_vertex(hI, k)));
     const int rb = T.face_begin(hR, r), nr = T.face_begin(hR, r + 1) - rb;
     int src = 0;
-    for (int m = 0; m < nr && cnt > 0; ++m) {
-        const int m1 = (m + 1 >= nr) ? m + 1 - nr : m + 1, m2 = (m + 2 >= nr) ? m + 2 - nr : m + 2;
-        const V3 w0 = ld3(WR, T.face_vertex(hR, rb + m));
-        const V3 w1 = ld3(WR, T.face_vertex(hR, rb + m1));
-        const V3 w2 = ld3(WR, T.face_vertex(hR, rb + m2));
-        V3 s = cross(w1 - w0, n);
-        if (dot(s, w2 - w0) > 0.0f) s = -s;
-        cnt = clip_polygon(C, src, cnt, w0, s, src ^ 1);
-        src ^= 1;
+    if (nr <= 4) {
+        // triangles and quads: the reference face's vertices are loaded ONCE, all in flight together (as written, every
+        // side plane re-loads three of them through the face index list: four dependent global-load latencies in a row)
+        V3 wv[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) wv[m] = ld3(WR, T.face_vertex(hR, rb + (m < nr ? m : 0)));
+        auto pick = [&](int k) {  // wv[k] for a run-time k (registers cannot be indexed: three selects per component)
+            const V3 lo = k & 1 ? wv[1] : wv[0], hi = k & 1 ? wv[3] : wv[2];
+            return k & 2 ? hi : lo;
+        };
+#pragma unroll 1
+        for (int m = 0; m < nr && cnt > 0; ++m) {  // rolled: ONE inlined copy of clip_polygon
+            const int m1 = (m + 1 >= nr) ? m + 1 - nr : m + 1, m2 = (m + 2 >= nr) ? m + 2 - nr : m + 2;
+            const V3 w0 = pick(m), w1 = pick(m1), w2 = pick(m2);
+            V3 s = cross(w1 - w0, n);
+            if (dot(s, w2 - w0) > 0.0f) s = -s;
+            cnt = clip_polygon(C, src, cnt, w0, s, src ^ 1);
+            src ^= 1;
+        }
+    } else {
+        for (int m = 0; m < nr && cnt > 0; ++m) {
+            const int m1 = (m + 1 >= nr) ? m + 1 - nr : m + 1, m2 = (m + 2 >= nr) ? m + 2 - nr : m + 2;
+            const V3 w0 = ld3(WR, T.face_vertex(hR, rb + m));
+            const V3 w1 = ld3(WR, T.face_vertex(hR, rb + m1));
+            const V3 w2 = ld3(WR, T.face_vertex(hR, rb + m2));
+            V3 s = cross(w1 - w0, n);
+            if (dot(s, w2 - w0) > 0.0f) s = -s;
+            cnt = clip_polygon(C, src, cnt, w0, s, src ^ 1);
+            src ^= 1;
+        }
     }
     // keep points strictly below the reference plane (compacted into the other buffer)
     const int dst = src ^ 1;
