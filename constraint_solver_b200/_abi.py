@@ -22,6 +22,8 @@ XPBD_ERR_CAPACITY = -3
 XPBD_ERR_SINGULAR = -4
 XPBD_ERR_STATE = -5
 XPBD_MAX_MANIFOLD = 4
+XPBD_STATIC_MAX_BODIES = 4096        # limits of xpbd_solve_batch_static (include/xpbd_b200.h)
+XPBD_STATIC_MAX_CONSTRAINTS = 32768
 
 # numpy mirrors of the C records (all C-contiguous, no padding surprises: checked below)
 RIGID_DTYPE = np.dtype(
@@ -134,6 +136,7 @@ _PROTOTYPES = {
     "xpbd_rigid_frame_batch": (C.c_int, [_VP, C.c_int64, _VP]),
     "xpbd_ground_batch": (C.c_int, [_VP, _VP, C.c_int64, C.POINTER(PolytopeC), _VP, _VP]),
     "xpbd_solve_batch": (C.c_int, [_VP, C.c_int64, _VP, _VP, C.c_int32, C.c_double, C.c_double]),
+    "xpbd_solve_batch_static": (C.c_int, [_VP, C.c_int64, _VP, _VP, C.c_int32, C.c_double, C.c_double]),
     "xpbd_face_axes_separation_batch": (C.c_int, [_VP, _VP, C.c_int64, C.POINTER(PolytopeC), C.POINTER(PolytopeC), _VP, _VP]),
     "xpbd_edge_axes_separation_batch": (C.c_int, [_VP, _VP, C.c_int64, C.POINTER(PolytopeC), C.POINTER(PolytopeC), _VP, _VP]),
     "xpbd_sat_manifold_batch": (C.c_int, [_VP, _VP, C.c_int64, C.POINTER(PolytopeC), C.POINTER(PolytopeC), _VP, _VP, _VP]),

@@ -3,6 +3,7 @@
 // face/edge_axes_separation, the finished sat) as its own CUDA kernel over n independent items.
 // Host records are the reference's AoS f64; the kernels round to fp32 on load and widen on store.
 #include <cstring>
+#include <mutex>
 
 #include "xpbd_host_math.hpp"
 #include "xpbd_internal.hpp"
@@ -449,3 +450,77 @@ int xpbd_fp32_peak_microbench(int32_t device, int32_t use_fma, double* tflops) {
 }
 
 }  // extern "C"
+
+// ---- xpbd_solve_batch without any allocation: working copies in a file-scope device array -----------------------------
+// No counterpart in the reference; added for callers that must not call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernel (solve_kernel) and same
+// arithmetic as xpbd_solve_batch; only where the device-side working copies live differs.
+//
+// g_static_scratch is part of the library's device image: every GPU that loads the library holds these 3.2 MiB until the
+// process exits.  In HOST code the name below is only a host-side stand-in for the symbol, not a device address; the
+// address the kernel gets comes from cudaGetSymbolAddress, asked once per device with that device current.
+namespace {
+
+constexpr size_t kStaticRigidBytes = (size_t)XPBD_STATIC_MAX_BODIES * sizeof(xpbd_rigid);             // 4096 x 304
+constexpr size_t kStaticConsBytes = (size_t)XPBD_STATIC_MAX_CONSTRAINTS * sizeof(xpbd_constraint);    // 32768 x 64
+constexpr size_t kStaticCountBytes = (size_t)XPBD_STATIC_MAX_BODIES * sizeof(int32_t);
+constexpr size_t kStaticConsOffset = kStaticRigidBytes;
+constexpr size_t kStaticCountOffset = kStaticConsOffset + kStaticConsBytes;
+constexpr size_t kStaticScratchBytes = kStaticCountOffset + kStaticCountBytes;
+static_assert(sizeof(xpbd_rigid) == 304 && sizeof(xpbd_constraint) == 64, "record sizes of include/xpbd_b200.h");
+static_assert(kStaticConsOffset % 256 == 0 && kStaticCountOffset % 256 == 0, "sub-buffers stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mutex;                                  // set-up only; the calls themselves are not serialised
+unsigned char* g_static_ptr[kStaticMaxDevices] = {};        // device address of g_static_scratch on each device
+
+// Device address of the scratch array on the CURRENT device (looked up once per device).
+int static_scratch(unsigned char** out) {
+    int dev = 0;
+    XPBD_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kStaticMaxDevices) return fail(XPBD_ERR_CAPACITY, "device ordinal %d outside [0, %d)", dev, kStaticMaxDevices);
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_ptr[dev]) {
+        void* p = nullptr;
+        XPBD_CUDA_TRY(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) return fail(XPBD_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        g_static_ptr[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = g_static_ptr[dev];
+    return XPBD_OK;
+}
+
+}  // namespace
+
+extern "C" int xpbd_solve_batch_static(xpbd_rigid* rigids, int64_t n, const xpbd_constraint* constraints, const int32_t* counts,
+                                       int32_t stride, double dt, double compliance) {
+    if (!rigids || n < 0) return fail(XPBD_ERR_INVALID, "bad rigids/n");
+    if (!constraints || !counts || stride <= 0) return fail(XPBD_ERR_INVALID, "bad constraints/counts/stride");
+    if (n > XPBD_STATIC_MAX_BODIES)
+        return fail(XPBD_ERR_CAPACITY, "xpbd_solve_batch_static: n = %lld bodies, the static scratch holds at most %d "
+                    "(use xpbd_solve_batch, which allocates)", (long long)n, XPBD_STATIC_MAX_BODIES);
+    if (n * (int64_t)stride > XPBD_STATIC_MAX_CONSTRAINTS)
+        return fail(XPBD_ERR_CAPACITY, "xpbd_solve_batch_static: n * stride = %lld constraint slots, the static scratch holds at "
+                    "most %d (use xpbd_solve_batch, which allocates)", (long long)(n * (int64_t)stride), XPBD_STATIC_MAX_CONSTRAINTS);
+    for (int64_t i = 0; i < n; ++i)
+        if (counts[i] < 0 || counts[i] > stride) return fail(XPBD_ERR_INVALID, "counts[%lld] outside [0, stride]", (long long)i);
+    if (int rc = need_device()) return rc;
+    if (n == 0) return XPBD_OK;
+    unsigned char* base = nullptr;
+    if (int rc = static_scratch(&base)) return rc;
+    double* d_rigids = reinterpret_cast<double*>(base);
+    double* d_cons = reinterpret_cast<double*>(base + kStaticConsOffset);
+    int32_t* d_counts = reinterpret_cast<int32_t*>(base + kStaticCountOffset);
+    // The array keeps the previous call's contents.  Nothing in it has to start at zero: the kernel reads records [0, n),
+    // constraint slots [i * stride, i * stride + counts[i]) and counts [0, n) only, and all of those are overwritten by
+    // this call's copies before the launch (same default stream, in order).
+    XPBD_CUDA_TRY(cudaMemcpy(d_rigids, rigids, (size_t)n * sizeof(xpbd_rigid), cudaMemcpyHostToDevice));
+    XPBD_CUDA_TRY(cudaMemcpy(d_cons, constraints, (size_t)n * stride * sizeof(xpbd_constraint), cudaMemcpyHostToDevice));
+    XPBD_CUDA_TRY(cudaMemcpy(d_counts, counts, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice));
+    solve_kernel<<<BLOCKS(n)>>>(d_rigids, n, d_cons, d_counts, stride, (float)dt, (float)compliance);
+    XPBD_CUDA_TRY(cudaGetLastError());
+    XPBD_CUDA_TRY(cudaMemcpy(rigids, d_rigids, (size_t)n * sizeof(xpbd_rigid), cudaMemcpyDeviceToHost));
+    return XPBD_OK;
+}

@@ -223,6 +223,19 @@ int xpbd_ground_batch(const xpbd_rigid* rigids, const xpbd_frame* past, int64_t 
 /* solver::solve (src/solver.rs:19-27): body i sweeps constraints[i * stride .. + counts[i]). */
 int xpbd_solve_batch(xpbd_rigid* rigids, int64_t n, const xpbd_constraint* constraints, const int32_t* counts,
                      int32_t stride, double dt, double compliance);
+/* xpbd_solve_batch that allocates nothing.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same kernel and bit-identical results; the device-side working copies of rigids,
+ * constraints and counts live in a static device array of 3.2 MiB inside the library (held by every GPU that loads the
+ * library until the process exits) instead of cudaMalloc'ed buffers.  No cudaMalloc / cudaFree / allocating library
+ * routine is called.  Limits: n <= XPBD_STATIC_MAX_BODIES and n * stride <= XPBD_STATIC_MAX_CONSTRAINTS, otherwise
+ * XPBD_ERR_CAPACITY (xpbd_last_error says which).  All calls on one device share the array, which keeps the last call's
+ * contents (every byte the kernel reads is overwritten by the call first): calls that overlap on the GPU — other host
+ * threads, other streams — race; serialise them.  Runs on the current device's default stream and returns when done. */
+#define XPBD_STATIC_MAX_BODIES 4096
+#define XPBD_STATIC_MAX_CONSTRAINTS 32768
+int xpbd_solve_batch_static(xpbd_rigid* rigids, int64_t n, const xpbd_constraint* constraints, const int32_t* counts,
+                            int32_t stride, double dt, double compliance);
 /* collision::face_axes_separation (src/collision.rs:123-149) on n frame pairs. */
 int xpbd_face_axes_separation_batch(const xpbd_frame* frames_a, const xpbd_frame* frames_b, int64_t n,
                                     const xpbd_polytope* hull_a, const xpbd_polytope* hull_b, double* distance,

@@ -102,6 +102,8 @@ pub struct xpbd_batch {
 }
 
 pub const XPBD_MAX_MANIFOLD: usize = 4;
+pub const XPBD_STATIC_MAX_BODIES: i64 = 4096;
+pub const XPBD_STATIC_MAX_CONSTRAINTS: i64 = 32768;
 
 // Every entry point of include/xpbd_b200.h, in the header's order (tests/test_abi.py diffs names and argument counts).
 extern "C" {
@@ -141,6 +143,10 @@ extern "C" {
                              out: *mut xpbd_constraint, counts: *mut i32) -> c_int;
     pub fn xpbd_solve_batch(rigids: *mut xpbd_rigid, n: i64, constraints: *const xpbd_constraint, counts: *const i32,
                             stride: i32, dt: f64, compliance: f64) -> c_int;
+    /// No counterpart in the reference: `xpbd_solve_batch` with its device working copies in a static device array
+    /// (no cudaMalloc); at most 4096 bodies and 32768 constraint slots per call, calls must not overlap on the GPU.
+    pub fn xpbd_solve_batch_static(rigids: *mut xpbd_rigid, n: i64, constraints: *const xpbd_constraint, counts: *const i32,
+                                   stride: i32, dt: f64, compliance: f64) -> c_int;
     pub fn xpbd_face_axes_separation_batch(frames_a: *const xpbd_frame, frames_b: *const xpbd_frame, n: i64, hull_a: *const xpbd_polytope,
                                            hull_b: *const xpbd_polytope, distance: *mut f64, face: *mut i32) -> c_int;
     pub fn xpbd_edge_axes_separation_batch(frames_a: *const xpbd_frame, frames_b: *const xpbd_frame, n: i64, hull_a: *const xpbd_polytope,
