@@ -76,8 +76,16 @@ struct StagedParams {
 };
 
 // ---- stage 1: prepare (warp per world) -----------------------------------------------------------------
-// per-warp shared scratch, words per body: fpos 3, pfpos 3, finvp 3, cen 3, rot 4, prot 4, hull 1, vertex offset 1
-constexpr int kPrepWordsPerBody = 22;
+// Per-world shared scratch: kPrepSlots float4 per body, slot-major ([slot * B + body]: lanes over bodies read consecutive
+// float4, lanes on the same body broadcast).  What the vertex / ground / broadphase loops need of a body is then one or two
+// LDS.128 each instead of a dozen scalar loads and a hull-descriptor lookup:
+//   0 rot   rotation (v.x, v.y, v.z, s)                 3 prot  rotation at the start of the substep
+//   1 fpos  frame position | hull vertex info           4 pfpos past frame position | first flat vertex index (compact walk)
+//   2 cen   world centroid | bounding radius            5 finvp inverse frame position | hull id
+// (hull vertex info = word offset of the hull's float4 vertex array | n_verts << 20; integers travel as float bit patterns)
+constexpr int kPrepSlots = 6;
+constexpr int kPrepWordsPerBody = 4 * kPrepSlots;
+enum PrepSlot : int { kPsRot = 0, kPsFpos = 1, kPsCen = 2, kPsProt = 3, kPsPfpos = 4, kPsFinvp = 5 };
 
 #ifndef XPBD_PREP_MIN_BLOCKS
 #define XPBD_PREP_MIN_BLOCKS 4
@@ -101,11 +109,10 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
     const int gshift = grp * G;
     const unsigned gmask = G == 32 ? kFull : (((1u << (G & 31)) - 1u) << gshift);
     const unsigned below_me = (1u << gl) - 1u;
-    float* W = reinterpret_cast<float*>(smem) + P.hull_blob_bytes / 4 + (size_t)(warp * NG + grp) * kPrepWordsPerBody * B;
-    float* s_fpos = W; float* s_pfpos = W + 3 * B; float* s_finvp = W + 6 * B; float* s_cen = W + 9 * B;
-    float* s_rot = W + 12 * B; float* s_prot = W + 16 * B;
-    int* s_hull = reinterpret_cast<int*>(W + 20 * B);
-    int* s_voff = s_hull + B;  // compact vertex enumeration: vertices of the bodies before b (mixed-hull batches)
+    float4* W = reinterpret_cast<float4*>(smem + P.hull_blob_bytes / 4) + (size_t)(warp * NG + grp) * kPrepSlots * B;
+    float4* s_rot = W + kPsRot * B; float4* s_fpos = W + kPsFpos * B; float4* s_cen = W + kPsCen * B;
+    float4* s_prot = W + kPsProt * B; float4* s_pfpos = W + kPsPfpos * B; float4* s_finvp = W + kPsFinvp * B;
+    auto voff = [&](int b) { return __float_as_int(s_pfpos[b].w); };  // compact walk: vertices of the bodies before b
     uint32_t* pair_table = smem + P.hull_blob_bytes / 4 + (size_t)nwarps * NG * kPrepWordsPerBody * B;
     const int n_table = P.pair_table_len;
     if (n_table > 0) {
@@ -121,7 +128,6 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
         const int64_t world = w0 + grp;
         const bool valid = world < P.n_worlds;  // odd world count: the second half of the last warp idles
         const int64_t g0 = world * B;
-        bool overflow = false;
         // --- bodies: save past, Rigid::integrate, frames (lanes over bodies)
         for (int b = gl; b < B && valid; b += G) {
             const int64_t g = g0 + b;
@@ -129,17 +135,22 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
             load_dyn(P.bodies, g, d);
             load_const(P.bodies, g, k);
             const Fr past = rigid_frame(d.position, d.rotation, k.center_of_mass);
+            const float4 prot4 = make_float4(d.rotation.x, d.rotation.y, d.rotation.z, d.rotation.s);
             P.S.ppos[g] = make_float4(d.position.x, d.position.y, d.position.z, 0.f);
-            P.S.prot[g] = make_float4(d.rotation.x, d.rotation.y, d.rotation.z, d.rotation.s);
-            sst3(s_pfpos, B, b, past.p); sstq(s_prot, B, b, d.rotation);
+            P.S.prot[g] = prot4;
+            s_prot[b] = prot4;
+            s_pfpos[b] = make_float4(past.p.x, past.p.y, past.p.z, 0.f);
             rigid_integrate(d, k, sc.dt * k.inverse_inertia, sc);
             store_dyn(P.bodies, g, d);
             const Fr frame = rigid_frame(d.position, d.rotation, k.center_of_mass);
             const Fr finv = frame_inverse(frame);
             const int h = P.hull_ids ? P.hull_ids[g] : 0;
-            const V3 c = frame * T.centroid(T.desc(h));
-            sst3(s_fpos, B, b, frame.p); sst3(s_finvp, B, b, finv.p); sst3(s_cen, B, b, c); sstq(s_rot, B, b, d.rotation);
-            s_hull[b] = h;
+            const HullDesc& hd = T.desc(h);
+            const V3 c = frame * T.centroid(hd);
+            s_rot[b] = make_float4(d.rotation.x, d.rotation.y, d.rotation.z, d.rotation.s);
+            s_fpos[b] = make_float4(frame.p.x, frame.p.y, frame.p.z, __int_as_float(hd.vert_off | (hd.n_verts << 20)));
+            s_cen[b] = make_float4(c.x, c.y, c.z, hd.radius);
+            s_finvp[b] = make_float4(finv.p.x, finv.p.y, finv.p.z, __int_as_float(h));
             P.S.fpos[g] = make_float4(frame.p.x, frame.p.y, frame.p.z, 0.f);
             P.S.finvp[g] = make_float4(finv.p.x, finv.p.y, finv.p.z, 0.f);
             P.S.cen[g] = make_float4(c.x, c.y, c.z, 0.f);
@@ -157,11 +168,11 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
                 int run = 0;
                 for (int b0 = 0; b0 < B; b0 += G) {
                     const int bb = b0 + gl;
-                    const int nv = (valid && bb < B) ? T.desc(s_hull[bb]).n_verts : 0;
+                    const int nv = (valid && bb < B) ? (__float_as_int(s_fpos[bb].w) >> 20) : 0;
                     int incl = nv;
 #pragma unroll
                     for (int o = 1; o < G; o <<= 1) { const int up = __shfl_up_sync(kFull, incl, o, G); if (gl >= o) incl += up; }
-                    if (valid && bb < B) s_voff[bb] = run + incl - nv;
+                    if (valid && bb < B) s_pfpos[bb].w = __int_as_float(run + incl - nv);
                     run += __shfl_sync(kFull, incl, G - 1, G);
                 }
                 total = (int)__reduce_max_sync(kFull, (unsigned)run);  // a warp-uniform trip count (two worlds per warp when G = 16)
@@ -173,24 +184,28 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
             for (int t0 = 0; t0 < total; t0 += G) {
                 bool has = false;
                 int vv = 0;
+                float4 fp = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (P.compact_verts) {
                     if (valid && b < B) {
-                        while (b + 1 < B && v >= s_voff[b + 1]) ++b;
-                        vv = v - s_voff[b];
-                        has = vv < T.desc(s_hull[b]).n_verts;  // false once the flat index has run past the last body
+                        while (b + 1 < B && v >= voff(b + 1)) ++b;
+                        vv = v - voff(b);
+                        fp = s_fpos[b];
+                        has = vv < (__float_as_int(fp.w) >> 20);  // false once the flat index has run past the last body
                     }
                 } else {
                     while (v >= maxV) { v -= maxV; ++b; }
                     vv = v;
-                    has = valid && b < B && v < T.desc(s_hull[b < B ? b : 0]).n_verts;
+                    has = valid && b < B;  // every hull of the batch has maxV vertices
+                    if (has) fp = s_fpos[b];
                 }
                 bool below = false;
                 V3 p = v3(0.f, 0.f, 0.f);
                 Fr frame;
                 if (has) {
-                    const HullDesc& hd = T.desc(s_hull[b]);
-                    frame.p = sld3(s_fpos, B, b); frame.q = sldq(s_rot, B, b);
-                    p = frame * T.vertex(hd, vv);
+                    const float4 rq = s_rot[b];
+                    const float4 lv = reinterpret_cast<const float4*>(smem + (__float_as_int(fp.w) & 0xfffff))[vv];
+                    frame.p = v3(fp.x, fp.y, fp.z); frame.q = q4(rq.w, rq.x, rq.y, rq.z);
+                    p = frame * v3(lv.x, lv.y, lv.z);
                     P.S.verts[(g0 + b) * maxV + vv] = make_float4(p.x, p.y, p.z, 0.f);
                     below = !(p.z >= 0.0f);
                 }
@@ -198,9 +213,10 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
                 if (below) {
                     const int idx = n_ground + __popc(m & below_me);
                     if (idx < P.S.capG) {
+                        const float4 pf = s_pfpos[b], pq = s_prot[b], fi = s_finvp[b];
                         Fr past, finv;
-                        past.p = sld3(s_pfpos, B, b); past.q = sldq(s_prot, B, b);
-                        finv.q = conjugate(frame.q); finv.p = sld3(s_finvp, B, b);
+                        past.p = v3(pf.x, pf.y, pf.z); past.q = q4(pq.w, pq.x, pq.y, pq.z);
+                        finv.q = conjugate(frame.q); finv.p = v3(fi.x, fi.y, fi.z);
                         const V3 target = v3(p.x, p.y, 0.0f);
                         const V3 correction = target - p;
                         const V3 delta = p - (past * (finv * p));
@@ -212,8 +228,6 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
                         float4* c = reinterpret_cast<float4*>(gc + (size_t)idx * kGroundWords);
                         c[0] = make_float4(__int_as_float(cons_head(kGround, b, -1)), p.x, p.y, p.z);
                         c[1] = make_float4(dir.x, dir.y, dir.z, dist);
-                    } else {
-                        overflow = true;
                     }
                 }
                 n_ground += __popc(m);
@@ -222,51 +236,48 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
         }
         // --- broadphase: bounding spheres about the hull centroids, pairs i<j in lexicographic order
         int n_pairs = 0;
+        bool overflow = n_ground > P.S.capG;  // uniform in the lane group: a ground contact found no slot
         if (P.body_body) {
             int4* pairs = P.S.pairs + (size_t)world * P.S.capP;
+            auto spheres_touch = [&](float4 a, float4 c) {  // a = sphere of body i, c = sphere of body j (i < j)
+                const V3 d = v3(c.x, c.y, c.z) - v3(a.x, a.y, a.z);
+                const float rsum = fadd(a.w, c.w);
+                return !(magnitude2(d) > fmul(rsum, rsum));
+            };
             if (n_table > 0) {
+                const int my_table = valid ? n_table : 0;
                 for (int p0 = 0; p0 < n_table; p0 += G) {
                     const int p = p0 + gl;
                     bool cand = false;
                     uint32_t ij = 0;
-                    if (valid && p < n_table) {
+                    if (p < my_table) {
                         ij = pair_table[p];
-                        const int i = ij & 0xffff, j = ij >> 16;
-                        const V3 d = sld3(s_cen, B, j) - sld3(s_cen, B, i);
-                        const float rsum = fadd(T.desc(s_hull[i]).radius, T.desc(s_hull[j]).radius);
-                        cand = !(magnitude2(d) > fmul(rsum, rsum));
+                        cand = spheres_touch(s_cen[ij & 0xffff], s_cen[ij >> 16]);
                     }
                     const unsigned m = (__ballot_sync(kFull, cand) & gmask) >> gshift;
                     if (cand) {
                         const int idx = n_pairs + __popc(m & below_me);
                         if (idx < P.S.capP) pairs[idx] = make_int4((int)ij, kNone, -1, 0);
-                        else overflow = true;
                     }
                     n_pairs += __popc(m);
                 }
             } else {
                 for (int i = 0; i + 1 < B; ++i) {
-                    const V3 ci = sld3(s_cen, B, i);
-                    const float ri = T.desc(s_hull[i]).radius;
+                    const float4 si = valid ? s_cen[i] : make_float4(0.f, 0.f, 0.f, 0.f);
                     for (int j0 = i + 1; j0 < B; j0 += G) {
                         const int j = j0 + gl;
-                        bool cand = false;
-                        if (valid && j < B) {
-                            const V3 d = sld3(s_cen, B, j) - ci;
-                            const float rsum = fadd(ri, T.desc(s_hull[j]).radius);
-                            cand = !(magnitude2(d) > fmul(rsum, rsum));
-                        }
+                        const bool cand = valid && j < B && spheres_touch(si, s_cen[j < B ? j : 0]);
                         const unsigned m = (__ballot_sync(kFull, cand) & gmask) >> gshift;
                         if (cand) {
                             const int idx = n_pairs + __popc(m & below_me);
                             if (idx < P.S.capP) pairs[idx] = make_int4(i | (j << 16), kNone, -1, 0);
-                            else overflow = true;
                         }
                         n_pairs += __popc(m);
                     }
                 }
             }
-            if (n_pairs > P.S.capP) n_pairs = P.S.capP;
+            overflow = overflow || n_pairs > P.S.capP;  // uniform in the lane group: a candidate found no slot
+            if (overflow) n_pairs = P.S.capP;
             // append this world's candidates to the global work list (order irrelevant: results land in the slots)
             unsigned base = 0;
             if (gl == 0 && n_pairs) base = atomicAdd(P.S.work_count, (unsigned)n_pairs);
@@ -274,10 +285,10 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
             __syncwarp();  // the pair slots written above are read back by other lanes
             for (int p = gl; p < n_pairs; p += G) {
                 const int ij = pairs[p].x;
-                P.S.worklist[base + p] = make_int4((int)(world * P.S.capP + p), ij, s_hull[ij & 0xffff] | (s_hull[ij >> 16] << 16), (int)world);
+                const int hi = __float_as_int(s_finvp[ij & 0xffff].w), hj = __float_as_int(s_finvp[ij >> 16].w);
+                P.S.worklist[base + p] = make_int4((int)(world * P.S.capP + p), ij, hi | (hj << 16), (int)world);
             }
         }
-        overflow = (__ballot_sync(kFull, overflow) & gmask) != 0;
         if (gl == 0 && valid) {
             P.S.n_ground[world] = n_ground < P.S.capG ? n_ground : P.S.capG;
             P.S.n_pairs[world] = n_pairs;
