@@ -816,6 +816,17 @@ static cudaError_t dev_alloc(T*& p, size_t n, size_t& total) {
     return cudaMalloc(reinterpret_cast<void**>(&p), bytes > 16 ? bytes : 16);
 }
 
+// Every registered hull is cube-shaped (8 vertices, 12 edges, 6 quads): the batch can run the cube schedules of the SAT stage.
+static bool all_cube_hulls(const xpbd_batch* b) {
+    bool all_cubes = !b->hulls.empty();
+    for (const HostHull& h : b->hulls) {
+        bool quads = h.face_offsets.size() == 7;
+        for (size_t f = 0; quads && f + 1 < h.face_offsets.size(); ++f) quads = h.face_offsets[f + 1] - h.face_offsets[f] == 4;
+        all_cubes = all_cubes && h.vertices.size() == 8 * 3 && h.edges.size() == 12 * 2 && quads;
+    }
+    return all_cubes;
+}
+
 static int build_staged(xpbd_batch* b, StagedState* st);
 // The state is published in b->world_scratch only once it is complete: a failed allocation / capacity check leaves no
 // half-built cache behind (the next step call starts over and reports the original error again).
@@ -889,12 +900,7 @@ static int build_staged(xpbd_batch* b, StagedState* st) {
     if (const char* e = std::getenv("XPBD_SAT_CULL")) cull = e[0] != '0';
     st->sat_fn = cull ? stage_sat_kernel<true> : stage_sat_kernel<false>;
     {
-        bool all_cubes = !b->hulls.empty();
-        for (const HostHull& h : b->hulls) {
-            bool quads = h.face_offsets.size() == 7;
-            for (size_t f = 0; quads && f + 1 < h.face_offsets.size(); ++f) quads = h.face_offsets[f + 1] - h.face_offsets[f] == 4;
-            all_cubes = all_cubes && h.vertices.size() == 8 * 3 && h.edges.size() == 12 * 2 && quads;
-        }
+        const bool all_cubes = all_cube_hulls(b);
         // Schedules of the SAT stage for all-cube batches (XPBD_SAT_SCHED, A/B runs): "thread" (default) = thread per
         // candidate, "dual" = two candidates per warp, "warp" = the generic warp-per-candidate kernel.
         const char* e = std::getenv("XPBD_SAT_SCHED");
@@ -927,11 +933,15 @@ static int build_staged(xpbd_batch* b, StagedState* st) {
 }
 
 // Number of world ranges a step call runs concurrently: the caller's choice (xpbd_batch_set_sub_batches), else
-// XPBD_SUB_BATCHES, else one range per 2^18 bodies (rounded) up to 4 (C3 and C4: 4).
+// XPBD_SUB_BATCHES, else one range per 2^18 bodies (rounded) up to 4 for all-cube batches (C3: 4) and up to 2 for
+// mixed-hull batches (C4: 2).  The ranges pay where the issue-bound thread-per-candidate SAT kernel of one range shares
+// the SMs with the latency-bound stages of the others; the warp-per-candidate kernel of mixed batches is latency-bound
+// itself and wants the whole SM (C4, measured: 1 range 1.07e9, 2 ranges 1.08e9, 4 ranges 1.04e9 body-substeps/s; two
+// ranges keep the per-range overlap of host copies with kernels in xpbd_batch_step_host_*).
 static int pick_sub_batches(const xpbd_batch* b) {
     int k = b->sub_batches;
     if (k <= 0) { if (const char* e = std::getenv("XPBD_SUB_BATCHES")) k = std::atoi(e); }
-    if (k <= 0) k = (int)std::min<int64_t>(4, (b->n_bodies + (1 << 17)) >> 18);  // rounded: C3's 10^6 bodies -> 4
+    if (k <= 0) k = (int)std::min<int64_t>(all_cube_hulls(b) ? 4 : 2, (b->n_bodies + (1 << 17)) >> 18);  // rounded: C3's 10^6 bodies -> 4
     k = std::max(1, std::min(k, kMaxSubBatches));
     return (int)std::min<int64_t>(k, std::max<int64_t>(1, b->desc.n_worlds));
 }
@@ -1009,10 +1019,12 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
     P.cand_stat = nullptr;
     const int n_sub = pick_sub_batches(b);
     if (int rc = ensure_sub_streams(b, st, n_sub)) return rc;
-    // Resident blocks per SM of the persistent SAT kernel: everything the registers allow when it runs alone, 2 when
-    // several ranges share the device (measured on C3 with 4 ranges: 2 -> 6.47e8, 3 -> 6.42e8, 4 -> 6.33e8 body-substeps/s).
-    // (the thread-per-candidate kernel has 128-thread blocks: the same 16 warps are 4 of them)
-    int occ_sat = n_sub > 1 ? std::min(st->occ_sat, std::max(2, 512 / st->sat_threads)) : st->occ_sat;
+    // Resident blocks per SM of the persistent SAT kernel: everything the registers allow when it runs alone or on a
+    // mixed-hull batch (C4 with 2 ranges: 4 blocks 1.08e9, 3 blocks 1.06e9, 2 blocks 1.01e9 body-substeps/s), 16 warps when
+    // several ranges of an all-cube batch share the device (round 1, C3 with 4 ranges of the two-per-warp kernel: 2 blocks
+    // of 256 -> 6.47e8, 3 -> 6.42e8, 4 -> 6.33e8; the thread-per-candidate kernel has 128-thread blocks: the same 16 warps
+    // are 4 of them).
+    int occ_sat = n_sub > 1 && all_cube_hulls(b) ? std::min(st->occ_sat, std::max(2, 512 / st->sat_threads)) : st->occ_sat;
     if (const char* e = std::getenv("XPBD_SAT_BLOCKS_PER_SM")) occ_sat = std::min(st->occ_sat, std::max(1, std::atoi(e)));
     const int total = substeps * n_frames;
     // The ranges wait for the batch stream only when something was enqueued there since the last step call
