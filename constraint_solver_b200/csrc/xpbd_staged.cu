@@ -741,13 +741,207 @@ __global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel
     if (lane == 0 && applied) atomicAdd(P.counters, (unsigned long long)applied);
 }
 
+// ---- stage 4, wide schedule: LW lanes (LW / 2 lane pairs) per world ---------------------------------------------------
+// The lane-pair kernel above walks a world's constraints one after the other; with 64 bodies, 32 joints and a few dozen
+// contacts per world (C4) that is one long dependent chain per lane pair and 1 000 warps for the whole device.  But
+// Gauss-Seidel only orders constraints that SHARE A BODY: constraint k reads and writes its own one or two bodies, so it
+// can run as soon as the last earlier constraint on either body is done, and any schedule that keeps that order per body
+// produces bit-identical state.  Per world and substep:
+//   ground contacts : every body's contacts are applied, in list order, by the lane that owns the body (body % LW);
+//   manifolds       : level[p] = 1 + max(level of the last earlier manifold on body a, on body b), computed serially by
+//                     one lane from the pair list (a few instructions per pair); the manifolds of one level touch disjoint
+//                     bodies and are dealt to the lane pairs, level after level;
+//   joints          : the same with their own levels (C4's 32 joints connect 64 different bodies: one level);
+//   derive          : lanes over bodies;
+//   velocity pass   : the manifolds again, same levels.
+// Between levels every lane writes its cached bodies back and the world's lanes meet (__syncwarp).  Per-contact
+// arithmetic is the lane-pair code of xpbd_solve.cuh, unchanged.
+constexpr int kSolveWideBlock = 128;
+#ifndef XPBD_SOLVE_WIDE_LANES
+#define XPBD_SOLVE_WIDE_LANES 8
+#endif
+constexpr int kSolveWideDefaultLanes = XPBD_SOLVE_WIDE_LANES;
+#ifndef XPBD_SOLVE_WIDE_MIN_BLOCKS
+#define XPBD_SOLVE_WIDE_MIN_BLOCKS 6  // 80 registers: no spills (64 spill a few words)
+#endif
+__host__ __device__ inline size_t solve_wide_group_words16(int B, int capP, int J) { return (size_t)((2 * B + capP + J + 1) & ~1); }
+
+XD int nth_set_bit(unsigned m, int r) { return (int)__fns(m, 0, r + 1); }  // position of the r-th (0-based) set bit
+
+template <int LW>
+__global__ void __launch_bounds__(kSolveWideBlock, XPBD_SOLVE_WIDE_MIN_BLOCKS) stage_solve_wide_kernel(StagedParams P) {
+    extern __shared__ __align__(16) uint16_t wide_smem[];
+    constexpr int NG = 32 / LW;  // worlds per warp
+    constexpr int NP = LW / 2;   // lane pairs per world
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const int grp = lane / LW, gl = lane % LW, gshift = grp * LW;
+    const unsigned gm = LW == 32 ? 0xffffffffu : (((1u << (LW & 31)) - 1u) << gshift);
+    const int side = lane & 1, q = gl >> 1;
+    const unsigned pm = 3u << (lane & ~1);
+    uint16_t* last_p = wide_smem + (size_t)(warp * NG + grp) * solve_wide_group_words16(P.B, P.S.capP, P.J);
+    uint16_t* last_j = last_p + P.B;
+    uint16_t* lvp = last_j + P.B;    // level of pair slot p (0: no contacts)
+    uint16_t* lvj = lvp + P.S.capP;  // level of joint j (0: inactive)
+    unsigned applied = 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {  // consumed by sat + manifold; the next substep appends again
+        if (P.cand_stat) atomicAdd(P.cand_stat, (unsigned long long)*P.S.work_count);
+        *P.S.work_count = 0;
+        P.S.work_count[2] = 0;
+    }
+    const StepConsts sc = P.sc;
+    for (int64_t w0 = ((int64_t)blockIdx.x * nwarps + warp) * NG; w0 < P.n_worlds; w0 += (int64_t)gridDim.x * nwarps * NG) {
+        const int64_t world = w0 + grp;
+        const bool valid = world < P.n_worlds;  // the last warp's spare groups run the loops below with zero trip counts
+        const int64_t g0 = world * P.B;
+        const int nB = valid ? P.B : 0, nJ = valid ? P.J : 0;
+        const int n_ground = valid ? P.S.n_ground[world] : 0, n_pairs = valid ? P.S.n_pairs[world] : 0;
+        int4* pairs = P.S.pairs + (size_t)world * P.S.capP;
+        float4* pc = P.S.pcons + (size_t)world * P.S.capP * kMaxManifold * 3;
+        const DeviceJoint* joints = P.joints + world * P.J;
+        // --- levels (lane 0: manifolds, lane 1: joints)
+        for (int b = gl; b < nB; b += LW) { last_p[b] = 0; last_j[b] = 0; }
+        __syncwarp(gm);
+        int max_lv = 0;
+        if (gl == 0) {
+            unsigned n = (unsigned)n_ground;
+            for (int p = 0; p < n_pairs; ++p) {
+                const int4 pr = pairs[p];
+                int lv = 0;
+                if (pr.w) {
+                    const int a = pr.x & 0xffff, b = pr.x >> 16;
+                    lv = 1 + max((int)last_p[a], (int)last_p[b]);
+                    last_p[a] = (uint16_t)lv; last_p[b] = (uint16_t)lv;
+                    max_lv = max(max_lv, lv);
+                    n += (unsigned)pr.w;
+                }
+                lvp[p] = (uint16_t)lv;
+            }
+            applied += n;
+        } else if (gl == 1) {
+            unsigned n = 0;
+            for (int j = 0; j < nJ; ++j) {
+                const int a = joints[j].body_a, b = joints[j].body_b;
+                int lv = 0;
+                if (a >= 0) {
+                    lv = 1 + max((int)last_j[a], b >= 0 ? (int)last_j[b] : 0);
+                    last_j[a] = (uint16_t)lv;
+                    if (b >= 0) last_j[b] = (uint16_t)lv;
+                    max_lv = max(max_lv, lv);
+                    ++n;
+                }
+                lvj[j] = (uint16_t)lv;
+            }
+            applied += n;
+        }
+        __syncwarp(gm);
+        const int max_lp = __shfl_sync(gm, max_lv, gshift), max_lj = __shfl_sync(gm, max_lv, gshift + 1);
+        // --- sweep: ground constraints, each body's by its owner lane in list order ...
+        {
+            CachedBody<false> C{P.bodies, g0};
+            const float4* gc = reinterpret_cast<const float4*>(P.S.gcons + (size_t)world * P.S.capG * kGroundWords);
+            for (int k = 0; k < n_ground; ++k) {
+                const float4 c0 = gc[2 * k];
+                const int a = head_a(__float_as_int(c0.x));
+                if (a % LW == gl) {
+                    const float4 c1 = gc[2 * k + 1];
+                    C.release(a); C.acquire(a);
+                    solve_ground(C, a, v3(c0.y, c0.z, c0.w), v3(c1.x, c1.y, c1.z), c1.w, sc);
+                }
+            }
+            C.flush();
+        }
+        __syncwarp(gm);
+        // --- ... then the manifolds, level by level ...
+        for (int lv = 1; lv <= max_lp; ++lv) {
+            CachedBody<false> C{P.bodies, g0};
+            for (int p0 = 0; p0 < n_pairs; p0 += LW) {
+                const bool mine = p0 + gl < n_pairs && lvp[p0 + gl] == lv;
+                const unsigned m = (__ballot_sync(gm, mine) & gm) >> gshift;
+                const int nm = __popc(m);
+                for (int r = q; r < nm; r += NP) {
+                    const int p = p0 + nth_set_bit(m, r);
+                    const int cnt = pairs[p].w;
+                    int active_mask = 0;
+                    for (int k = 0; k < cnt; ++k) {
+                        const float4* c = pc + ((size_t)p * kMaxManifold + k) * 3;
+                        const float4 c0 = c[0], c1 = c[1], c2 = c[2];
+                        const int head = __float_as_int(c0.x);
+                        const int role = contact_role(side, head);
+                        const int me = role ? head_b(head) : head_a(head);
+                        C.release(me); __syncwarp(pm); C.acquire(me);
+                        const bool active = solve_contact(C, role, pm, me, role ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w),
+                                                          v3(c2.x, c2.y, c2.z), sc);
+                        active_mask |= (int)active << k;
+                    }
+                    if (side == 0 && active_mask) pairs[p].w = cnt | (active_mask << 8);
+                }
+            }
+            C.flush();
+            __syncwarp(gm);
+        }
+        // --- ... then the joints, level by level
+        for (int lv = 1; lv <= max_lj; ++lv) {
+            CachedBody<false> C{P.bodies, g0};
+            for (int j0 = 0; j0 < nJ; j0 += LW) {
+                const bool mine = j0 + gl < nJ && lvj[j0 + gl] == lv;
+                const unsigned m = (__ballot_sync(gm, mine) & gm) >> gshift;
+                const int nm = __popc(m);
+                for (int r = q; r < nm; r += NP) {
+                    const DeviceJoint jt = joints[j0 + nth_set_bit(m, r)];
+                    const int me = side ? jt.body_b : jt.body_a;
+                    C.release(me); __syncwarp(pm); C.acquire(me);
+                    solve_joint(C, side, pm, me, jt.body_b >= 0, side ? v3(jt.bx, jt.by, jt.bz) : v3(jt.ax, jt.ay, jt.az), jt.distance, sc);
+                }
+            }
+            C.flush();
+            __syncwarp(gm);
+        }
+        // --- Rigid::derive, lanes over bodies
+        {
+            GlobalBodies A{P.bodies, P.S.ppos, P.S.prot, g0};
+            for (int b = gl; b < nB; b += LW) derive_body(A, b, sc.dt);
+        }
+        __syncwarp(gm);
+        // --- velocity pass over the contacts that were active in the sweep, same levels
+        for (int lv = 1; lv <= max_lp; ++lv) {
+            CachedBody<true> C{P.bodies, g0};
+            for (int p0 = 0; p0 < n_pairs; p0 += LW) {
+                const bool mine = p0 + gl < n_pairs && lvp[p0 + gl] == lv;
+                const unsigned m = (__ballot_sync(gm, mine) & gm) >> gshift;
+                const int nm = __popc(m);
+                for (int r = q; r < nm; r += NP) {
+                    const int p = p0 + nth_set_bit(m, r);
+                    const int word = pairs[p].w, cnt = word & 0xff, active_mask = word >> 8;
+                    for (int k = 0; k < cnt; ++k) {
+                        if (!((active_mask >> k) & 1)) continue;
+                        const float4* c = pc + ((size_t)p * kMaxManifold + k) * 3;
+                        const float4 c0 = c[0], c1 = c[1], c2 = c[2];
+                        const int head = __float_as_int(c0.x);
+                        const int role = contact_role(side, head);
+                        const int me = role ? head_b(head) : head_a(head);
+                        C.release(me); __syncwarp(pm); C.acquire(me);
+                        velocity_contact(C, role, pm, me, role ? v3(c1.x, c1.y, c1.z) : v3(c0.y, c0.z, c0.w), v3(c2.x, c2.y, c2.z),
+                                         P.friction);
+                    }
+                }
+            }
+            C.flush();
+            __syncwarp(gm);
+        }
+    }
+    // one atomic per warp (lanes leave the loop at different times: reconverge first)
+    __syncwarp();
+    for (int o = 16; o > 0; o >>= 1) applied += __shfl_down_sync(0xffffffffu, applied, o);
+    if (lane == 0 && applied) atomicAdd(P.counters, (unsigned long long)applied);
+}
+
 // ---- host side -------------------------------------------------------------------------------------------------
 constexpr int kGraphMaxSubsteps = 256;  // longer chains (many frames per call) launch directly
 struct RangeGraphKey {    // everything the captured chain of one world range depends on (compared bytewise: zero-filled first)
     StagedParams params;  // of the range, cand_stat = nullptr
     int total;            // substeps in the chain
     int grid[4];
-    const void* fn[3];    // prepare, sat, manifold kernels
+    const void* fn[4];    // prepare, sat, manifold, solve kernels
 };
 struct RangeGraph {
     cudaGraphExec_t exec = nullptr;
@@ -773,6 +967,8 @@ struct StagedState {
     int prepare_lanes = 32, pair_table_len = 0;
     int n_sm = 148;
     int solve_blocks_per_sm = 0;  // grid-stride over worlds: resident blocks per SM (occupancy), XPBD_SOLVE_BLOCKS_PER_SM overrides
+    int solve_lanes_default = 2;  // lanes per world of the solve stage: 2 = stage_solve_kernel, 4 ... 32 = stage_solve_wide_kernel
+    size_t smem_solve_wide = 0;   // per block of kSolveWideBlock threads at the default lane count
     int occ_prepare = 1, occ_sat = 1, occ_manifold = 1;
     // Sub-batches: the worlds are split into n_sub contiguous ranges, each stepped by its own chain of launches on its
     // own stream (forked from / joined into the batch stream inside one step call).  Worlds are independent, so the
@@ -877,6 +1073,12 @@ static int build_staged(xpbd_batch* b, StagedState* st) {
         XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_solve, stage_solve_kernel, 128, 0));
         st->solve_blocks_per_sm = occ_solve < 6 ? occ_solve : 6;  // measured on C3: 6 resident blocks beat 7, 8 and an unbounded grid (L2 working set)
         if (const char* e = std::getenv("XPBD_SOLVE_BLOCKS_PER_SM")) st->solve_blocks_per_sm = std::atoi(e);
+        // Worlds of more than 16 bodies get the wide schedule (several lane pairs per world, constraints on disjoint bodies
+        // in parallel); small worlds keep one lane pair each (C3's stack is one dependent chain: nothing to spread).
+        st->solve_lanes_default = B > 16 ? kSolveWideDefaultLanes : 2;
+        // few large worlds: more lanes per world until the device has about one resident thread per slot (C4: 16 k worlds -> 8)
+        while (B > 16 && st->solve_lanes_default < 32 && st->n_worlds * st->solve_lanes_default < (int64_t)n_sm * XPBD_SOLVE_WIDE_MIN_BLOCKS * kSolveWideBlock)
+            st->solve_lanes_default *= 2;
     }
     // prepare: warps per block limited by the per-warp body scratch
     st->prepare_lanes = B <= 16 ? 16 : 32;  // lanes per world
@@ -1026,6 +1228,25 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
     // are 4 of them).
     int occ_sat = n_sub > 1 && all_cube_hulls(b) ? std::min(st->occ_sat, std::max(2, 512 / st->sat_threads)) : st->occ_sat;
     if (const char* e = std::getenv("XPBD_SAT_BLOCKS_PER_SM")) occ_sat = std::min(st->occ_sat, std::max(1, std::atoi(e)));
+    // Schedule of the solve stage: XPBD_SOLVE_LANES = 2 (lane pair per world), 4, 8, 16, 32 (wide) overrides the default.
+    int solve_lanes = st->solve_lanes_default;
+    if (const char* e = std::getenv("XPBD_SOLVE_LANES")) solve_lanes = std::atoi(e);
+    void (*solve_fn)(StagedParams) = stage_solve_kernel;
+    switch (solve_lanes) {
+        case 4: solve_fn = stage_solve_wide_kernel<4>; break;
+        case 8: solve_fn = stage_solve_wide_kernel<8>; break;
+        case 16: solve_fn = stage_solve_wide_kernel<16>; break;
+        case 32: solve_fn = stage_solve_wide_kernel<32>; break;
+        default: solve_lanes = 2; break;
+    }
+    size_t smem_solve = 0;
+    int occ_solve_wide = 1;
+    if (solve_fn != stage_solve_kernel) {
+        smem_solve = (size_t)(kSolveWideBlock / solve_lanes) * solve_wide_group_words16(B, st->buf.capP, P.J) * sizeof(uint16_t);
+        if (smem_solve > 48 * 1024) XPBD_CUDA_TRY(cudaFuncSetAttribute(solve_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_solve));
+        XPBD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_solve_wide, solve_fn, kSolveWideBlock, smem_solve));
+        if (occ_solve_wide < 1) return fail(XPBD_ERR_CAPACITY, "worlds too large for the wide solve schedule (%zu bytes of shared memory per block)", smem_solve);
+    }
     const int total = substeps * n_frames;
     // The ranges wait for the batch stream only when something was enqueued there since the last step call
     // (b->fork_needed); otherwise each range simply continues behind its own previous frame.
@@ -1084,6 +1305,8 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
         const int grid_manifold = (int)std::min<int64_t>((nw * S.capP + 127) / 128, (int64_t)st->n_sm * st->occ_manifold);
         unsigned grid_solve = (unsigned)((2 * nw + 127) / 128);
         if (st->solve_blocks_per_sm > 0) grid_solve = std::min(grid_solve, (unsigned)(st->solve_blocks_per_sm * st->n_sm));
+        if (solve_fn != stage_solve_kernel)
+            grid_solve = (unsigned)std::min<int64_t>((nw * solve_lanes + kSolveWideBlock - 1) / kSolveWideBlock, (int64_t)st->n_sm * occ_solve_wide);
         // the chain of this range: overflow flags reset, then `total` substeps of (prepare, sat, manifold, solve)
         auto enqueue_chain = [&](bool with_events) -> int {
             XPBD_CUDA_TRY(cudaMemsetAsync(S.overflow, 0, (size_t)nw * sizeof(int), stream));
@@ -1098,7 +1321,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
                 if (timed) cudaEventRecord(b->ev_stage[2], stream);
                 if (P.body_body) st->manifold_fn<<<grid_manifold, kManifoldThreads, st->smem_manifold, stream>>>(Q);
                 if (timed) cudaEventRecord(b->ev_stage[3], stream);
-                stage_solve_kernel<<<grid_solve, 128, 0, stream>>>(Q);
+                solve_fn<<<grid_solve, 128, smem_solve, stream>>>(Q);
                 if (timed) cudaEventRecord(b->ev_stage[4], stream);
             }
             XPBD_CUDA_TRY(cudaGetLastError());
@@ -1111,6 +1334,7 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
             key.params = Q; key.params.cand_stat = nullptr;
             key.total = total; key.grid[0] = grid_prepare; key.grid[1] = grid_sat; key.grid[2] = grid_manifold; key.grid[3] = (int)grid_solve;
             key.fn[0] = (const void*)st->prepare_fn; key.fn[1] = (const void*)st->sat_fn; key.fn[2] = (const void*)st->manifold_fn;
+            key.fn[3] = (const void*)solve_fn;
             if (!G.exec || std::memcmp(&G.key, &key, sizeof key) != 0) {
                 G.release();
                 cudaGraph_t graph = nullptr;

@@ -209,6 +209,32 @@ def test_sub_batches_do_not_change_results(world_path, k):
     _check(scenes.c3_stack(5, n_cubes=3), [CUBE], 10, 10, sub_batches=8)  # more ranges than worlds
 
 
+@pytest.mark.parametrize("lanes", [2, 4, 8, 16, 32])
+def test_solve_lane_counts_do_not_change_results(world_path, lanes, monkeypatch):
+    """XPBD_SOLVE_LANES: the solve stage with `lanes` lanes per world (2 = one lane pair walks the world's constraints in
+    order; 4 ... 32 = stage_solve_wide_kernel: ground contacts by body, manifolds and joints by dependency level, spread
+    over lanes / 2 lane pairs).  Constraints that share a body keep their order, so every schedule is bit-identical to the
+    oracle: a dense mixed-hull pile with joints (many independent manifolds), joint chains through shared bodies, a stack
+    (one dependent chain), ragged world counts."""
+    if world_path == "fused":
+        pytest.skip("a schedule of the staged pipeline")
+    monkeypatch.setenv("XPBD_SOLVE_LANES", str(lanes))
+    init, hulls, ids, joints = scenes.c4_pile(11, spacing=1.5)  # dense lattice: body-body contacts from the first frames
+    _, c = _check(init, hulls, 20, 20, hull_ids=ids, joints=joints)
+    assert c["manifolds"] > 0
+    # joints that share bodies (a chain 0-1-2-...-7 in index order, then a second pass in reverse order): several levels
+    n, B = 7, 8
+    init = scenes.c3_stack(n, n_cubes=B)
+    jt = np.zeros((n, 2 * (B - 1)), dtype=_abi.JOINT_DTYPE)
+    jt["body_a"] = -1
+    order = [(i, i + 1) for i in range(B - 1)] + [(i + 1, i) for i in reversed(range(B - 1))]
+    for j, (a, b) in enumerate(order):
+        jt["body_a"][:, j] = a; jt["body_b"][:, j] = b
+        jt["anchor_a"][:, j] = (0.5, 0.5, 0.5); jt["anchor_b"][:, j] = (0.5, 0.5, 0.5); jt["distance"][:, j] = 1.05
+    _check(init, [CUBE], 15, 20, joints=jt)
+    _check(scenes.c3_stack(37), [CUBE], 20, 20)
+
+
 def test_sub_batches_back_to_back_step_calls(world_path):
     """Between back-to-back step calls the world ranges do not wait for each other (no per-frame barrier); an
     asynchronous upload in between makes them wait for the batch stream again.  Same bits as the oracle either way."""
