@@ -758,7 +758,7 @@ __global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel
 // arithmetic is the lane-pair code of xpbd_solve.cuh, unchanged.
 constexpr int kSolveWideBlock = 128;
 #ifndef XPBD_SOLVE_WIDE_LANES
-#define XPBD_SOLVE_WIDE_LANES 8
+#define XPBD_SOLVE_WIDE_LANES 16  // C4 with 3 world ranges: 16 lanes 1.31e9, 8 lanes 1.29e9 body-substeps/s
 #endif
 constexpr int kSolveWideDefaultLanes = XPBD_SOLVE_WIDE_LANES;
 #ifndef XPBD_SOLVE_WIDE_MIN_BLOCKS
@@ -1076,7 +1076,7 @@ static int build_staged(xpbd_batch* b, StagedState* st) {
         // Worlds of more than 16 bodies get the wide schedule (several lane pairs per world, constraints on disjoint bodies
         // in parallel); small worlds keep one lane pair each (C3's stack is one dependent chain: nothing to spread).
         st->solve_lanes_default = B > 16 ? kSolveWideDefaultLanes : 2;
-        // few large worlds: more lanes per world until the device has about one resident thread per slot (C4: 16 k worlds -> 8)
+        // few large worlds: more lanes per world until the device has about one resident thread per slot (C4: 16 k worlds -> 16)
         while (B > 16 && st->solve_lanes_default < 32 && st->n_worlds * st->solve_lanes_default < (int64_t)n_sm * XPBD_SOLVE_WIDE_MIN_BLOCKS * kSolveWideBlock)
             st->solve_lanes_default *= 2;
     }
@@ -1135,15 +1135,15 @@ static int build_staged(xpbd_batch* b, StagedState* st) {
 }
 
 // Number of world ranges a step call runs concurrently: the caller's choice (xpbd_batch_set_sub_batches), else
-// XPBD_SUB_BATCHES, else one range per 2^18 bodies (rounded) up to 4 for all-cube batches (C3: 4) and up to 2 for
-// mixed-hull batches (C4: 2).  The ranges pay where the issue-bound thread-per-candidate SAT kernel of one range shares
+// XPBD_SUB_BATCHES, else one range per 2^18 bodies (rounded) up to 4 for all-cube batches (C3: 4) and up to 3 for
+// mixed-hull batches (C4: 3).  The ranges pay where the issue-bound thread-per-candidate SAT kernel of one range shares
 // the SMs with the latency-bound stages of the others; the warp-per-candidate kernel of mixed batches is latency-bound
-// itself and wants the whole SM (C4, measured: 1 range 1.07e9, 2 ranges 1.08e9, 4 ranges 1.04e9 body-substeps/s; two
-// ranges keep the per-range overlap of host copies with kernels in xpbd_batch_step_host_*).
+// itself and runs at full occupancy (C4 with the wide solve schedule, measured: 1 range 1.14e9, 2 ranges 1.27e9, 3 ranges
+// 1.31e9, 4 ranges 1.28e9 body-substeps/s; the ranges also overlap host copies with kernels in xpbd_batch_step_host_*).
 static int pick_sub_batches(const xpbd_batch* b) {
     int k = b->sub_batches;
     if (k <= 0) { if (const char* e = std::getenv("XPBD_SUB_BATCHES")) k = std::atoi(e); }
-    if (k <= 0) k = (int)std::min<int64_t>(all_cube_hulls(b) ? 4 : 2, (b->n_bodies + (1 << 17)) >> 18);  // rounded: C3's 10^6 bodies -> 4
+    if (k <= 0) k = (int)std::min<int64_t>(all_cube_hulls(b) ? 4 : 3, (b->n_bodies + (1 << 17)) >> 18);  // rounded: C3's 10^6 bodies -> 4
     k = std::max(1, std::min(k, kMaxSubBatches));
     return (int)std::min<int64_t>(k, std::max<int64_t>(1, b->desc.n_worlds));
 }
