@@ -275,9 +275,26 @@ XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int 
 //     dot(axis, w - foot) = s * dot(c, w - foot) / |c|,   s = sign of dot(c, foot - centroid_A)   (the reference's flip).
 // Stage 1 (all pairs; no sqrt, no reciprocal, no support scan): cull when s * dot(c, w - foot) < -(|T| + M) |c|, compared
 // in squared form, where M bounds every rounding difference between this estimate and the fp32 value the reference
-// arithmetic produces (about 4e-6 * R for coordinates up to R; M = 4e-5 * (1 + R), ten times that).  A pair whose flip sign
-// is not clear-cut (|dot(c, foot - centroid_A)| <= M |c|) is kept.  A pair with |c|^2 == 0 or NaN (parallel edges; NaN
-// vertices) has a NaN distance in the reference arithmetic, which can never win: culled.
+// arithmetic produces.  A pair whose flip sign is not clear-cut (|dot(c, foot - centroid_A)| <= M |c|) is kept.  A pair with
+// |c|^2 == 0 or NaN (parallel edges; NaN vertices) has a NaN distance in the reference arithmetic, which can never win: culled.
+//
+// The margin.  u = 2^-24, R = largest |coordinate| of the two hulls' world vertices (so |v| <= sqrt(3) R and
+// |B_v - foot| <= 2 sqrt(3) R), c = the fp32 cross product (the cull and the reference form it by the same expression from
+// the same fp32 edge vectors: identical bits), c^ = c / |c| exactly.  Worst case, every error aligned:
+//   reference  axis = fl(normalize(c)) = c^ (1 + e), |e| <= 4.5 u per component (|c|^2 3u, sqrt, reciprocal, product);
+//              its direction c' differs from c^ by <= 9 u per component, its length from 1 by <= 4.5 u;
+//              sb   = min_v fl(axis . B_v)                        : 3 u sqrt(3) R = 5.2 u R   of rounding per dot
+//              disp = +-fl|fl(axis fl(fl(foot . axis) / fl(axis . axis)))| : 12.1 u R (quotient) + 6.1 u R (length)
+//              distance = fl(sb - disp) = c' . (B_v* - foot) + (|axis| - 1) c' . B_v* + the roundings above
+//                       <= c^ . (w - foot) + (4.5 sqrt(3) + 5.2 + 18.2) u R + 9 u |w - foot|   <=  c^ . (w - foot) + 62.4 u R;
+//   estimate   fl(c . fl(w - foot)) / |c| (thread kernel) is within 4 u |w - foot| <= 13.9 u R of c^ . (w - foot);
+//              fl(c . w) - fl(c . foot) (warp kernels) within 10.4 u R; the squared comparison adds a few u RELATIVE to tm.
+// Hence estimate < T - M implies distance < T as soon as M >= 76.3 u R = 4.6e-6 R.  The sign of the flip is the sign of
+// c^ . (foot - centroid_A) whenever that exceeds ~8 u |foot - centroid_A| (reference) resp. 10.4 u R (estimate) — far below M.
+// M = 1e-5 (1 + R): 2.2 x that worst-case bound for large R, more below (round 1 used 4e-5 (1 + R); on C3's resting stacks,
+// whose contact depths are 1e-5 ... 3e-4, the tighter margin halves the pairs that reach stage 2: 16.2 -> 8.6 per candidate).
+// tests/test_sat_fuzz.py sweeps penetrations and gaps ulp by ulp through 0 and through T at offsets 0 / 1e3 / 1e4 for every
+// schedule with and without the cull.
 // Stage 2 (survivors, through the warp-private queue): the reference's arithmetic for that pair, unchanged — axis,
 // flip, support scan of A, plane displacement, support scan of B, "first strict maximum" tie rule.
 // Two witnesses are used (witness_vertices: B's deepest vertex below A's best face and a second deep vertex far from it);
@@ -285,16 +302,19 @@ XD void edge_query_t(const int2* EA, const int2* EB, int nA_rt, int nEa_rt, int 
 #ifdef XPBD_CULL_STATS
 __device__ unsigned long long g_cull_stats[3 + 40];  // + histogram of pairs kept per query (capped at 39)  // edge queries, pairs kept by stage 1, pairs seen (debug builds: scripts/cull_stats.sh)
 #endif
+#ifndef XPBD_CULL_MARGIN
+#define XPBD_CULL_MARGIN 1e-5f
+#endif
 struct EdgeCull {
     float T;    // min(0, kRelEdge * face_max + kAbsTol)
-    float M;    // rounding margin, 4e-5 * (1 + largest |coordinate| of the two hulls' world vertices)
+    float M;    // rounding margin, XPBD_CULL_MARGIN * (1 + largest |coordinate| of the two hulls' world vertices)
     V3 w1, w2;  // witnesses: two world-space vertices of B (the smaller of the two bounds is used)
 };
 XD EdgeCull make_edge_cull(float da, float db, float max_abs_coord, V3 witness1, V3 witness2) {
     EdgeCull c;
     const float face_max = da > db ? da : db;
     c.T = fminf(0.0f, fadd(fmul(kRelEdge, face_max), kAbsTol));
-    c.M = 4e-5f * (1.0f + max_abs_coord);
+    c.M = XPBD_CULL_MARGIN * (1.0f + max_abs_coord);
     c.w1 = witness1;
     c.w2 = witness2;
     return c;

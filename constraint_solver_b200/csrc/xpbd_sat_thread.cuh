@@ -105,6 +105,9 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
     uint32_t rkey = 0;
     int2 wi = make_int2(0, 0);
     V3 CA;
+#ifdef XPBD_CULL_STATS
+    unsigned st_class = 0, st_class_culled = 0, st_fb_ill = 0, st_fb_well = 0, st_kept_ill = 0, st_kept_well = 0, st_walk_a = 0, st_walk_b = 0;
+#endif
     {
         V3 WA[8], WB[8], L[8];
 #pragma unroll
@@ -186,7 +189,15 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
                         const float us = f < 0.0f ? -fmaxf(u1, u2) : fminf(u1, u2);
                         const float Np = -us - h1, Gp = fabsf(f) - g0;
                         class_culled = Np > 0.0f && Np * Np > K * c2 && Gp > 0.0f && Gp * Gp > Kf * c2 && c2 > c2min;
+#ifdef XPBD_CULL_STATS
+                        ++st_class; st_class_culled += class_culled; if (!class_culled) { if (c2 > c2min) ++st_fb_well; else ++st_fb_ill; }
+#endif
                     }
+#ifdef XPBD_CULL_STATS
+                    const uint32_t bits_before = bits;
+                    bool ill = false;
+                    if (boxB) { const V3 c = cross(edge_a, eb[4 * j]); ill = !(dot(c, c) > c2min); }
+#endif
                     if (!class_culled) {
 #pragma unroll
                         for (int k = 4 * j; k < 4 * j + 4; ++k) {
@@ -200,6 +211,9 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
                             bits |= (keep ? 1u : 0u) << ((int)(perm >> (4 * k)) & 15);
                         }
                     }
+#ifdef XPBD_CULL_STATS
+                    { const unsigned kept = __popc(bits ^ bits_before); if (ill) st_kept_ill += kept; else st_kept_well += kept; }
+#endif
                 }
                 *S.mask(ia) = bits;
             }
@@ -238,7 +252,13 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
             float sa = dot(axis, XA[0]);
 #pragma unroll
             for (int v = 1; v < 8; ++v) sa = fmaxf(sa, dot(axis, XA[v]));
+#ifdef XPBD_CULL_STATS
+            ++st_walk_a;
+#endif
             if (sa > dot(foot, axis)) continue;
+#ifdef XPBD_CULL_STATS
+            ++st_walk_b;
+#endif
             const float disp = plane_displacement(foot, axis);
             float sb = dot(axis, XB[0]);
 #pragma unroll
@@ -248,6 +268,14 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
         }
         de = best; ep = bi;
         if (!(de >= 0.0f)) pf = choose_feature(da, fa, db, fb, de, ep);
+#ifdef XPBD_CULL_STATS
+        atomicAdd(&g_cull_stats[0], 1ull); atomicAdd(&g_cull_stats[1], (unsigned long long)(st_kept_ill + st_kept_well)); atomicAdd(&g_cull_stats[2], 144ull);
+        atomicAdd(&g_cull_stats[3 + 20], (unsigned long long)st_class); atomicAdd(&g_cull_stats[3 + 21], (unsigned long long)st_class_culled);
+        atomicAdd(&g_cull_stats[3 + 22], (unsigned long long)st_fb_ill); atomicAdd(&g_cull_stats[3 + 23], (unsigned long long)st_fb_well);
+        atomicAdd(&g_cull_stats[3 + 24], (unsigned long long)st_kept_ill); atomicAdd(&g_cull_stats[3 + 25], (unsigned long long)st_kept_well);
+        atomicAdd(&g_cull_stats[3 + 26], (unsigned long long)st_walk_a); atomicAdd(&g_cull_stats[3 + 27], (unsigned long long)st_walk_b);
+        atomicAdd(&g_cull_stats[3 + 28], (unsigned long long)(pf.feature == kEdgeEdge));
+#endif
     }
 done:
     P.S.pairs[d.x].y = pf.feature;
@@ -262,6 +290,24 @@ __global__ void __launch_bounds__(kSatThreadBlock, XPBD_SAT_THREAD_MIN_BLOCKS) s
     const HullTable T{smem};
     SatThreadScratch S;
     S.col = reinterpret_cast<float4*>(smem + P.hull_blob_bytes / 4) + threadIdx.x;
+    if (P.by_level) {
+        // Candidates in (pair slot, world) order: the 32 candidates of a warp are the SAME pair slot of 32 consecutive worlds.
+        // In a batch of similar worlds (C3: pair slot p is the contact between cubes p and p + 1 of every stack) they take the
+        // same branches — the same classes culled, the same number of survivors to walk — where work-list order (the pairs of
+        // three or four worlds side by side) mixes the shallow top contacts with the deep bottom ones in every warp.
+        const unsigned nw = (unsigned)P.n_worlds, max_pairs = P.S.work_count[1];
+        const unsigned long long total = (unsigned long long)max_pairs * nw;
+        for (unsigned long long it = blockIdx.x * blockDim.x + threadIdx.x; it < total; it += gridDim.x * blockDim.x) {
+            const unsigned p = (unsigned)(it / nw), w = (unsigned)(it - (unsigned long long)p * nw);
+            if (p >= (unsigned)P.S.n_pairs[w]) continue;
+            const unsigned slot = w * (unsigned)P.S.capP + p;
+            const int ij = P.S.pairs[slot].x;
+            int hulls = 0;
+            if (P.hull_ids) hulls = P.hull_ids[(int64_t)w * P.B + (ij & 0xffff)] | (P.hull_ids[(int64_t)w * P.B + (ij >> 16)] << 16);
+            sat_thread_candidate<kCull>(P, T, make_int4((int)slot, ij, hulls, (int)w), S);
+        }
+        return;
+    }
     const unsigned count = *P.S.work_count;
     for (unsigned it = blockIdx.x * blockDim.x + threadIdx.x; it < count; it += gridDim.x * blockDim.x)
         sat_thread_candidate<kCull>(P, T, P.S.worklist[it], S);

@@ -44,7 +44,7 @@ struct StagedBuffers {
     int* n_pairs = nullptr;   // per world
     float4* pcons = nullptr;  // per (world, pair slot) x kMaxManifold x 3 float4
     int4* worklist = nullptr;  // per candidate: (world * capP + pair slot, i | j << 16, hull_i | hull_j << 16, world)
-    uint32_t* work_count = nullptr;  // [0] candidates of this substep
+    uint32_t* work_count = nullptr;  // [0] candidates of this substep, [1] largest pair count of a world, [2] stage_sat_kernel's cursor
     int* overflow = nullptr;         // per world
     int maxV = 0, capG = 0, capP = 0;
     size_t bytes = 0;
@@ -71,6 +71,7 @@ struct StagedParams {
     int body_body;
     int pair_table_len;  // B(B-1)/2 when stage_prepare keeps the pair table in shared memory, else 0
     int compact_verts;   // hulls with different vertex counts: stage_prepare enumerates (body, vertex) through a prefix sum
+    int by_level;        // all-cube batches: candidates enumerated in (pair slot, world) order by the SAT and manifold kernels; no work list
     unsigned long long* counters;  // [0] constraints, [1] overflow worlds, [2] tma fallbacks
     unsigned long long* cand_stat;  // non-null on the last substep of a step call: += candidates of this launch (statistics)
 };
@@ -278,15 +279,24 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
             }
             overflow = overflow || n_pairs > P.S.capP;  // uniform in the lane group: a candidate found no slot
             if (overflow) n_pairs = P.S.capP;
-            // append this world's candidates to the global work list (order irrelevant: results land in the slots)
-            unsigned base = 0;
-            if (gl == 0 && n_pairs) base = atomicAdd(P.S.work_count, (unsigned)n_pairs);
-            base = __shfl_sync(kFull, base, gshift);
-            __syncwarp();  // the pair slots written above are read back by other lanes
-            for (int p = gl; p < n_pairs; p += G) {
-                const int ij = pairs[p].x;
-                const int hi = __float_as_int(s_finvp[ij & 0xffff].w), hj = __float_as_int(s_finvp[ij >> 16].w);
-                P.S.worklist[base + p] = make_int4((int)(world * P.S.capP + p), ij, hi | (hj << 16), (int)world);
+            if (P.by_level) {
+                // no work list: the SAT and manifold kernels enumerate (pair slot, world) up to the largest pair count of a
+                // world, kept in work_count[1] (never reset: an upper bound is all they need, and an atomic is issued only when
+                // a world raises it — none in steady state, where the work-list append is one atomic per world on ONE
+                // address: 100 k serialised L2 atomics per C3 substep)
+                if (gl == 0 && (unsigned)n_pairs > *reinterpret_cast<volatile unsigned*>(P.S.work_count + 1))
+                    atomicMax(P.S.work_count + 1, (unsigned)n_pairs);
+            } else {
+                // append this world's candidates to the global work list (order irrelevant: results land in the slots)
+                unsigned base = 0;
+                if (gl == 0 && n_pairs) base = atomicAdd(P.S.work_count, (unsigned)n_pairs);
+                base = __shfl_sync(kFull, base, gshift);
+                __syncwarp();  // the pair slots written above are read back by other lanes
+                for (int p = gl; p < n_pairs; p += G) {
+                    const int ij = pairs[p].x;
+                    const int hi = __float_as_int(s_finvp[ij & 0xffff].w), hj = __float_as_int(s_finvp[ij >> 16].w);
+                    P.S.worklist[base + p] = make_int4((int)(world * P.S.capP + p), ij, hi | (hj << 16), (int)world);
+                }
             }
         }
         if (gl == 0 && valid) {
@@ -539,6 +549,20 @@ __global__ void __launch_bounds__(kManifoldThreads, XPBD_MANIFOLD_MIN_BLOCKS) st
     // clip polygons live in shared memory (thread-private arrays would be local memory: ~0.5 KB per candidate of
     // L2/HBM round trips, measured as 3x the stage's algorithmic traffic)
     ClipShared<CAP, kManifoldThreads> clip{reinterpret_cast<float*>(smem) + P.hull_blob_bytes / 4 + threadIdx.x};
+    if (P.by_level) {
+        // no work list (see stage_prepare_kernel): (world, pair slot) enumerated up to the largest pair count of a world.
+        // World-major here — the threads of a warp work on the pairs of the same few worlds and share their vertices and
+        // frames through the L1 ((pair slot, world) order, which pays in the SAT kernel, measured 0.251 vs 0.195 ms here).
+        const unsigned nw = (unsigned)P.n_worlds, max_pairs = P.S.work_count[1];
+        const unsigned long long total = (unsigned long long)max_pairs * nw;
+        for (unsigned long long it = blockIdx.x * blockDim.x + threadIdx.x; it < total; it += gridDim.x * blockDim.x) {
+            const unsigned w = (unsigned)(it / max_pairs), p = (unsigned)(it - (unsigned long long)w * max_pairs);
+            if (p >= (unsigned)P.S.n_pairs[w]) continue;
+            const uint32_t slot = w * (uint32_t)P.S.capP + p;
+            manifold_candidate(P, T, slot, P.S.pairs[slot], clip);
+        }
+        return;
+    }
     for (unsigned it = blockIdx.x * blockDim.x + threadIdx.x; it < count; it += gridDim.x * blockDim.x) {
         const uint32_t slot = (uint32_t)P.S.worklist[it].x;
         manifold_candidate(P, T, slot, P.S.pairs[slot], clip);
@@ -649,9 +673,8 @@ __global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel
     const int lane = threadIdx.x & 31;
     const int side = lane & 1;
     const unsigned pm = 3u << (lane & ~1);
-    unsigned applied = 0;
+    unsigned applied = 0, cands = 0;
     if (blockIdx.x == 0 && threadIdx.x == 0) {  // consumed by sat + manifold; the next substep appends again
-        if (P.cand_stat) atomicAdd(P.cand_stat, (unsigned long long)*P.S.work_count);  // statistics (summed over sub-batches)
         *P.S.work_count = 0;
         P.S.work_count[2] = 0;  // stage_sat_kernel's cursor
     }
@@ -661,6 +684,7 @@ __global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel
     for (int64_t world = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 1; world < P.n_worlds;
          world += ((int64_t)gridDim.x * blockDim.x) >> 1) {
         const int n_ground = P.S.n_ground[world], n_pairs = P.S.n_pairs[world];
+        cands += (unsigned)n_pairs;
         int4* pairs = P.S.pairs + (size_t)world * P.S.capP;
         float4* pc = P.S.pcons + (size_t)world * P.S.capP * kMaxManifold * 3;
         {
@@ -734,11 +758,12 @@ __global__ void __launch_bounds__(128, XPBD_SOLVE_MIN_BLOCKS) stage_solve_kernel
         }
         __syncwarp(pm);
     }
-    if (side) applied = 0;
+    if (side) { applied = 0; cands = 0; }
     // one atomic per warp (lanes leave the loop at different times: reconverge first)
     __syncwarp();
-    for (int o = 16; o > 0; o >>= 1) applied += __shfl_down_sync(0xffffffffu, applied, o);
+    for (int o = 16; o > 0; o >>= 1) { applied += __shfl_down_sync(0xffffffffu, applied, o); cands += __shfl_down_sync(0xffffffffu, cands, o); }
     if (lane == 0 && applied) atomicAdd(P.counters, (unsigned long long)applied);
+    if (lane == 0 && cands && P.cand_stat) atomicAdd(P.cand_stat, (unsigned long long)cands);  // statistics: candidate pairs of this substep
 }
 
 // ---- stage 4, wide schedule: LW lanes (LW / 2 lane pairs) per world ---------------------------------------------------
@@ -782,9 +807,8 @@ __global__ void __launch_bounds__(kSolveWideBlock, XPBD_SOLVE_WIDE_MIN_BLOCKS) s
     uint16_t* last_j = last_p + P.B;
     uint16_t* lvp = last_j + P.B;    // level of pair slot p (0: no contacts)
     uint16_t* lvj = lvp + P.S.capP;  // level of joint j (0: inactive)
-    unsigned applied = 0;
+    unsigned applied = 0, cands = 0;
     if (blockIdx.x == 0 && threadIdx.x == 0) {  // consumed by sat + manifold; the next substep appends again
-        if (P.cand_stat) atomicAdd(P.cand_stat, (unsigned long long)*P.S.work_count);
         *P.S.work_count = 0;
         P.S.work_count[2] = 0;
     }
@@ -804,6 +828,7 @@ __global__ void __launch_bounds__(kSolveWideBlock, XPBD_SOLVE_WIDE_MIN_BLOCKS) s
         int max_lv = 0;
         if (gl == 0) {
             unsigned n = (unsigned)n_ground;
+            cands += (unsigned)n_pairs;
             for (int p = 0; p < n_pairs; ++p) {
                 const int4 pr = pairs[p];
                 int lv = 0;
@@ -931,8 +956,9 @@ __global__ void __launch_bounds__(kSolveWideBlock, XPBD_SOLVE_WIDE_MIN_BLOCKS) s
     }
     // one atomic per warp (lanes leave the loop at different times: reconverge first)
     __syncwarp();
-    for (int o = 16; o > 0; o >>= 1) applied += __shfl_down_sync(0xffffffffu, applied, o);
+    for (int o = 16; o > 0; o >>= 1) { applied += __shfl_down_sync(0xffffffffu, applied, o); cands += __shfl_down_sync(0xffffffffu, cands, o); }
     if (lane == 0 && applied) atomicAdd(P.counters, (unsigned long long)applied);
+    if (lane == 0 && cands && P.cand_stat) atomicAdd(P.cand_stat, (unsigned long long)cands);
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------
@@ -1216,6 +1242,9 @@ int step_world_staged(xpbd_batch* b, float frame_dt, int substeps, int n_frames)
     P.body_body = b->desc.body_body_contacts;
     P.pair_table_len = st->pair_table_len;
     P.compact_verts = 0;
+    // (pair slot, world) enumeration instead of a work list: with the thread-per-candidate SAT kernel (XPBD_SAT_ORDER=list|level, A/B runs)
+    P.by_level = st->sat_fn == stage_sat_thread_kernel<true> || st->sat_fn == stage_sat_thread_kernel<false>;
+    if (const char* e = std::getenv("XPBD_SAT_ORDER")) P.by_level = P.by_level && std::strcmp(e, "list") != 0;
     for (const HostHull& h : b->hulls) if ((int)(h.vertices.size() / 3) != H.max_verts) P.compact_verts = 1;
     P.counters = b->d_counters;
     P.cand_stat = nullptr;
