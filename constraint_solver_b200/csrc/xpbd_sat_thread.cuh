@@ -148,22 +148,36 @@ XD void sat_thread_candidate(const StagedParams& P, const HullTable& T, int4 d, 
 #pragma unroll
             for (int k = 0; k < 12; ++k) { const int2 e = EB[(int)(perm >> (4 * k)) & 15]; eb[k] = S.vert(8 + e.y) - S.vert(8 + e.x); }
             // Class-level cull (box-like B).  The world-space vectors of B's parallel edges are the same real vector up to the
-            // fp32 rounding of their end points.  With u = 2^-24, rho = largest |object-space vertex| of B and R = largest
-            // |world coordinate|, frame * vertex = (qv x (qv x v + v s)) 2 + v + p carries at most 49 u rho + u R of rounding
-            // per component (worst case, every operation's error aligned), so two parallel edge vectors differ by at most
-            // beta = 200 u rho + 4 u R per component (4 end points + the two subtractions), i.e. by sqrt(3) beta in length.
-            // Hence c_p = edge_a x b_p differs from +-c_rep by at most e_c = |a| (sqrt(3) beta + rounding of the two cross
-            // products), and with N' = -us_rep - e_c max|d_i| - tm e_c and G' = |f_rep| - e_c |dC| - M e_c the conditions
+            // fp32 rounding of their end points: b_p = +-(b_rep + delta_p).  The spread beta = max |delta_p| (per component) is
+            // MEASURED on the twelve vectors in registers (nearly equal numbers subtract exactly; typically a few 1e-7 — the
+            // a-priori bound 200 u rho + 4 u R used before was ~50 x larger and sent half of the cullable classes of a resting
+            // stack to the per-pair tests).  Then c_p = edge_a x b_p differs from +-c_rep by at most
+            //     e_c = |a| (sqrt(3) beta + 4 sqrt(3) u |b|)        (the second term: fp32 rounding of the two cross products,
+            //                                                        2 u |a| |b| per component each, |b| <= 2 radius)
+            // in length, and with N' = -us_rep - e_c max|d_i| - tm e_c and G' = |f_rep| - e_c |dC| - M e_c the conditions
             //     N' > tm |c_rep|,  G' > M |c_rep|,  |c_rep| > 2 e_c
             // imply, for each of the four pairs, exactly the per-pair conditions below (us < 0, us^2 > K c2, f^2 > Kf c2,
             // c2 > 1e-24) in real arithmetic — the flip sign of every pair equals the representative's (up to the pair's
             // edge orientation, which cancels in s c).  One test then drops four pairs; a class that is not provably
-            // droppable (the contact's own classes, nearly parallel classes whose cross product is rounding noise,
-            // far-away coordinates) falls back to the per-pair tests, so nothing is decided differently — only sooner.
+            // droppable (the contact's own classes, nearly parallel classes whose cross product is rounding noise) falls back
+            // to the per-pair tests, so nothing is decided differently — only sooner.
             // (Lengths through sqrt.approx, rounded up by 1e-5.)
-            const float rhoB = 1.00001f * sqrt_approx(hB.cx * hB.cx + hB.cy * hB.cy + hB.cz * hB.cz) + hB.radius;
-            const float beta = 1.25e-5f * rhoB + 3e-7f * __int_as_float((int)rkey);  // 200 u = 1.19e-5, 4 u = 2.4e-7
-            const float e_unit = 1.7321f * beta + 8e-7f * hB.radius;                  // per unit length of edge_a
+            float beta = 0.0f;
+            if (boxB) {
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                    const V3 r = eb[4 * j];
+#pragma unroll
+                    for (int k = 4 * j + 1; k < 4 * j + 4; ++k) {
+                        const V3 e = eb[k];
+                        const bool opposite = e.x * r.x + e.y * r.y + e.z * r.z < 0.0f;
+                        const float dx = opposite ? e.x + r.x : e.x - r.x, dy = opposite ? e.y + r.y : e.y - r.y, dz = opposite ? e.z + r.z : e.z - r.z;
+                        beta = fmaxf(beta, fmaxf(fabsf(dx), fmaxf(fabsf(dy), fabsf(dz))));
+                    }
+                }
+                beta = beta != beta ? FLT_MAX : beta;  // NaN vertices: no class is droppable
+            }
+            const float e_unit = 1.7322f * beta + 9e-7f * hB.radius;  // per unit length of edge_a
 #pragma unroll 1
             for (int ia = 0; ia < 12; ++ia) {
                 const int2 ea = EA[ia];
