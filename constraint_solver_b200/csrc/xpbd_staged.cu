@@ -1169,7 +1169,12 @@ static int build_staged(xpbd_batch* b, StagedState* st) {
 static int pick_sub_batches(const xpbd_batch* b) {
     int k = b->sub_batches;
     if (k <= 0) { if (const char* e = std::getenv("XPBD_SUB_BATCHES")) k = std::atoi(e); }
-    if (k <= 0) k = (int)std::min<int64_t>(all_cube_hulls(b) ? 4 : 3, (b->n_bodies + (1 << 17)) >> 18);  // rounded: C3's 10^6 bodies -> 4
+    if (k <= 0) {
+        k = (int)std::min<int64_t>(all_cube_hulls(b) ? 4 : 3, (b->n_bodies + (1 << 17)) >> 18);  // rounded: C3's 10^6 bodies -> 4
+        // xpbd_batch_step_host_rigid moves 608 bytes per body over PCIe: the first range's upload and the last range's
+        // download are exposed, so twice as many, half as large ranges (C3: e2e_rigid_f64 8.9e8 -> 9.3e8; device time -1 %)
+        if (b->io_rigid_in || b->io_rigid_out) k *= 2;
+    }
     k = std::max(1, std::min(k, kMaxSubBatches));
     return (int)std::min<int64_t>(k, std::max<int64_t>(1, b->desc.n_worlds));
 }
