@@ -233,6 +233,31 @@ def test_solve_lane_counts_do_not_change_results(world_path, lanes, monkeypatch)
         jt["anchor_a"][:, j] = (0.5, 0.5, 0.5); jt["anchor_b"][:, j] = (0.5, 0.5, 0.5); jt["distance"][:, j] = 1.05
     _check(init, [CUBE], 15, 20, joints=jt)
     _check(scenes.c3_stack(37), [CUBE], 20, 20)
+    # random joint graphs, different in every world: repeated bodies, repeated pairs, world anchors (body_b = -1), inactive
+    # slots — arbitrary dependency DAGs for the level schedule; bodies on a loose lattice (24 per world: the wide default)
+    n, B, J = 9, 24, 40
+    rng = np.random.default_rng(1234 + lanes)
+    init = np.empty((n, B), dtype=_abi.RIGID_DTYPE)
+    base = scenes.cube_rigid(0.3); base.external_force = (0, 0, -3.0)
+    init[:] = base.rec
+    cell = np.stack(np.meshgrid(np.arange(4), np.arange(3), np.arange(2), indexing="ij"), axis=-1).reshape(B, 3)
+    init["position"] = cell[None, :, :] * 1.6 + np.array([0.0, 0.0, 0.4]) + rng.uniform(-0.05, 0.05, (n, B, 3))
+    init["velocity"] = rng.uniform(-0.3, 0.3, (n, B, 3))
+    jt = np.zeros((n, J), dtype=_abi.JOINT_DTYPE)
+    a = rng.integers(0, B, (n, J)); b = rng.integers(0, B, (n, J))
+    b = np.where(b == a, (b + 1) % B, b)
+    b = np.where(rng.random((n, J)) < 0.15, -1, b)            # anchored to the world
+    jt["body_a"] = np.where(rng.random((n, J)) < 0.1, -1, a)  # inactive
+    jt["body_b"] = b
+    jt["anchor_a"] = rng.uniform(0.0, 1.0, (n, J, 3))
+    jt["anchor_b"] = np.where((b == -1)[:, :, None], init["position"][np.arange(n)[:, None], a] + rng.uniform(-0.5, 1.5, (n, J, 3)),
+                              rng.uniform(0.0, 1.0, (n, J, 3)))
+    # rest lengths near the initial anchor distances (centres, roughly): the bodies are tugged about, not pulled into one clump
+    pa = init["position"][np.arange(n)[:, None], a] + 0.5
+    pb = np.where((b == -1)[:, :, None], jt["anchor_b"], init["position"][np.arange(n)[:, None], np.maximum(b, 0)] + 0.5)
+    jt["distance"] = np.linalg.norm(pb - pa, axis=2) * rng.uniform(0.9, 1.1, (n, J))
+    gpu, c = _check(init, [CUBE], 12, 20, joints=jt)
+    assert np.isfinite(xo.rigid38(gpu)).all() and c["constraints"] > 0
 
 
 def test_sub_batches_back_to_back_step_calls(world_path):
