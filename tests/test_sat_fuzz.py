@@ -279,3 +279,35 @@ def test_whole_scene_long_run_every_sat_variant_same_bits(variant, monkeypatch):
     got, c1 = _long_run(n, frames, variant, monkeypatch)
     assert c0 == c1
     assert np.array_equal(base.view(np.uint32), got.view(np.uint32))
+
+
+def _long_run_c4(n, frames, env, monkeypatch):
+    for k in ("XPBD_SAT_SCHED", "XPBD_SAT_CULL", "XPBD_SAT_ORDER", "XPBD_WORLD_PATH", "XPBD_SOLVE_LANES", "XPBD_SUB_BATCHES"):
+        monkeypatch.delenv(k, raising=False)
+    monkeypatch.setenv("XPBD_WORLD_PATH", "staged")
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    init, hulls, ids, joints = scenes.c4_pile(n)
+    with cs.Worlds(n, init.shape[1], device=0, body_body_contacts=True, joints_per_world=joints.shape[1]) as w:
+        for h in hulls:
+            w.add_hull(h)
+        w.set_hulls(ids)
+        w.set_joints(joints)
+        w.upload(init)
+        w.integrate(scenes.FRAME_DT, 20, frames)
+        st = w.stats()
+        assert st["overflow_worlds"] == 0 and st["nan_worlds"] == 0
+        return w.download_dynamic().copy(), st["constraints"]
+
+
+@pytest.mark.parametrize("variant", [{"XPBD_SAT_CULL": "0"}, {"XPBD_SOLVE_LANES": "2"}, {"XPBD_SOLVE_LANES": "32", "XPBD_SUB_BATCHES": "1"}],
+                         ids=["nocull", "solve-lane-pair", "solve-32-lanes-one-range"])
+def test_mixed_hull_scene_long_run_every_variant_same_bits(variant, monkeypatch):
+    """The same for the C4 scene (1 024 piles of 64 mixed QuickHull hulls + joints, 50 frames: the piles land from frame 19 on
+    and the candidate count peaks around frame 34): the warp-per-candidate SAT kernel with and without the witness cull, the
+    solve stage as one lane pair per world and as 16 / 32 lanes per world by dependency level — bit-identical final states."""
+    n, frames = 1024, 50
+    base, c0 = _long_run_c4(n, frames, {}, monkeypatch)
+    got, c1 = _long_run_c4(n, frames, variant, monkeypatch)
+    assert c0 == c1
+    assert np.array_equal(base.view(np.uint32), got.view(np.uint32))
