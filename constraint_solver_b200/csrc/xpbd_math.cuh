@@ -10,10 +10,20 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <cstdio>
 
 namespace xpbd {
 
 #define XD __device__ __forceinline__
+
+// Index checks of the debug build `make variant NAME=bounds EXTRA=-DXPBD_BOUNDS` (compute-sanitizer is not available on the
+// GPU pool): a failed check prints its location and traps, which surfaces as a CUDA error at the next synchronisation.
+// scripts/gpu_bounds.sh runs the parity tests on that library.  Compiled out of the product build.
+#ifdef XPBD_BOUNDS
+#define XPBD_CHECK(cond) do { if (!(cond)) { printf("XPBD_CHECK failed: %s (%s:%d, block %d thread %d)\n", #cond, __FILE__, __LINE__, (int)blockIdx.x, (int)threadIdx.x); __trap(); } } while (0)
+#else
+#define XPBD_CHECK(cond) do { } while (0)
+#endif
 
 XD float fadd(float a, float b) { return __fadd_rn(a, b); }
 XD float fsub(float a, float b) { return __fsub_rn(a, b); }

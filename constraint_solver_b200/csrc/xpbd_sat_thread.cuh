@@ -313,9 +313,11 @@ __global__ void __launch_bounds__(kSatThreadBlock, XPBD_SAT_THREAD_MIN_BLOCKS) s
         const unsigned long long total = (unsigned long long)max_pairs * nw;
         for (unsigned long long it = blockIdx.x * blockDim.x + threadIdx.x; it < total; it += gridDim.x * blockDim.x) {
             const unsigned p = (unsigned)(it / nw), w = (unsigned)(it - (unsigned long long)p * nw);
+            XPBD_CHECK(w < nw && max_pairs <= (unsigned)P.S.capP);
             if (p >= (unsigned)P.S.n_pairs[w]) continue;
             const unsigned slot = w * (unsigned)P.S.capP + p;
             const int ij = P.S.pairs[slot].x;
+            XPBD_CHECK((ij & 0xffff) < P.B && (ij >> 16) < P.B);
             int hulls = 0;
             if (P.hull_ids) hulls = P.hull_ids[(int64_t)w * P.B + (ij & 0xffff)] | (P.hull_ids[(int64_t)w * P.B + (ij >> 16)] << 16);
             sat_thread_candidate<kCull>(P, T, make_int4((int)slot, ij, hulls, (int)w), S);

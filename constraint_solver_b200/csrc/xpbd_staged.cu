@@ -203,6 +203,8 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
                 V3 p = v3(0.f, 0.f, 0.f);
                 Fr frame;
                 if (has) {
+                    XPBD_CHECK(b >= 0 && b < B && vv >= 0 && vv < maxV && vv < (__float_as_int(fp.w) >> 20));
+                    XPBD_CHECK(((__float_as_int(fp.w) & 0xfffff) + 4 * vv + 4) * 4 <= (int)P.hull_blob_bytes);
                     const float4 rq = s_rot[b];
                     const float4 lv = reinterpret_cast<const float4*>(smem + (__float_as_int(fp.w) & 0xfffff))[vv];
                     frame.p = v3(fp.x, fp.y, fp.z); frame.q = q4(rq.w, rq.x, rq.y, rq.z);
@@ -253,6 +255,7 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
                     uint32_t ij = 0;
                     if (p < my_table) {
                         ij = pair_table[p];
+                        XPBD_CHECK((int)(ij & 0xffff) < B && (int)(ij >> 16) < B && (ij & 0xffff) < (ij >> 16));
                         cand = spheres_touch(s_cen[ij & 0xffff], s_cen[ij >> 16]);
                     }
                     const unsigned m = (__ballot_sync(kFull, cand) & gmask) >> gshift;
@@ -284,6 +287,7 @@ __global__ void __launch_bounds__(256, XPBD_PREP_MIN_BLOCKS) stage_prepare_kerne
                 // world, kept in work_count[1] (never reset: an upper bound is all they need, and an atomic is issued only when
                 // a world raises it — none in steady state, where the work-list append is one atomic per world on ONE
                 // address: 100 k serialised L2 atomics per C3 substep)
+                XPBD_CHECK(n_pairs >= 0 && n_pairs <= P.S.capP);
                 if (gl == 0 && (unsigned)n_pairs > *reinterpret_cast<volatile unsigned*>(P.S.work_count + 1))
                     atomicMax(P.S.work_count + 1, (unsigned)n_pairs);
             } else {
@@ -557,6 +561,7 @@ __global__ void __launch_bounds__(kManifoldThreads, XPBD_MANIFOLD_MIN_BLOCKS) st
         const unsigned long long total = (unsigned long long)max_pairs * nw;
         for (unsigned long long it = blockIdx.x * blockDim.x + threadIdx.x; it < total; it += gridDim.x * blockDim.x) {
             const unsigned w = (unsigned)(it / max_pairs), p = (unsigned)(it - (unsigned long long)w * max_pairs);
+            XPBD_CHECK(w < nw && max_pairs <= (unsigned)P.S.capP);
             if (p >= (unsigned)P.S.n_pairs[w]) continue;
             const uint32_t slot = w * (uint32_t)P.S.capP + p;
             manifold_candidate(P, T, slot, P.S.pairs[slot], clip);
@@ -834,6 +839,7 @@ __global__ void __launch_bounds__(kSolveWideBlock, XPBD_SOLVE_WIDE_MIN_BLOCKS) s
                 int lv = 0;
                 if (pr.w) {
                     const int a = pr.x & 0xffff, b = pr.x >> 16;
+                    XPBD_CHECK(a < P.B && b < P.B && a != b && pr.w > 0 && pr.w <= kMaxManifold && p < P.S.capP);
                     lv = 1 + max((int)last_p[a], (int)last_p[b]);
                     last_p[a] = (uint16_t)lv; last_p[b] = (uint16_t)lv;
                     max_lv = max(max_lv, lv);
@@ -848,6 +854,7 @@ __global__ void __launch_bounds__(kSolveWideBlock, XPBD_SOLVE_WIDE_MIN_BLOCKS) s
                 const int a = joints[j].body_a, b = joints[j].body_b;
                 int lv = 0;
                 if (a >= 0) {
+                    XPBD_CHECK(a < P.B && b < P.B);
                     lv = 1 + max((int)last_j[a], b >= 0 ? (int)last_j[b] : 0);
                     last_j[a] = (uint16_t)lv;
                     if (b >= 0) last_j[b] = (uint16_t)lv;
@@ -867,6 +874,7 @@ __global__ void __launch_bounds__(kSolveWideBlock, XPBD_SOLVE_WIDE_MIN_BLOCKS) s
             for (int k = 0; k < n_ground; ++k) {
                 const float4 c0 = gc[2 * k];
                 const int a = head_a(__float_as_int(c0.x));
+                XPBD_CHECK(a >= 0 && a < P.B && k < P.S.capG);
                 if (a % LW == gl) {
                     const float4 c1 = gc[2 * k + 1];
                     C.release(a); C.acquire(a);
@@ -885,6 +893,7 @@ __global__ void __launch_bounds__(kSolveWideBlock, XPBD_SOLVE_WIDE_MIN_BLOCKS) s
                 const int nm = __popc(m);
                 for (int r = q; r < nm; r += NP) {
                     const int p = p0 + nth_set_bit(m, r);
+                    XPBD_CHECK(p >= p0 && p < n_pairs && lvp[p] == lv);
                     const int cnt = pairs[p].w;
                     int active_mask = 0;
                     for (int k = 0; k < cnt; ++k) {
@@ -912,6 +921,7 @@ __global__ void __launch_bounds__(kSolveWideBlock, XPBD_SOLVE_WIDE_MIN_BLOCKS) s
                 const unsigned m = (__ballot_sync(gm, mine) & gm) >> gshift;
                 const int nm = __popc(m);
                 for (int r = q; r < nm; r += NP) {
+                    XPBD_CHECK(j0 + nth_set_bit(m, r) < nJ && lvj[j0 + nth_set_bit(m, r)] == lv);
                     const DeviceJoint jt = joints[j0 + nth_set_bit(m, r)];
                     const int me = side ? jt.body_b : jt.body_a;
                     C.release(me); __syncwarp(pm); C.acquire(me);
